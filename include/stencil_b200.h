@@ -1,0 +1,156 @@
+/* stencil_b200.h — C ABI of the B200 (sm_100a) stencil-sweep backend.
+ *
+ * This is the drop-in boundary for the reference's accelerator call
+ *   athread_spawn(SLAVE_FUN(stencil_iterate_X), &args); athread_join();
+ * (reference: src/stencil/stencil.cpp:34-53, kernel declarations
+ * src/stencil/slave/stencil_slave.hpp:26-46, argument block `struct Arguments`
+ * src/stencil/slave/stencil_slave.hpp:13-24).  Plain pointers and sizes only;
+ * no C++ or torch types cross this boundary.  Every function returns 0 on
+ * success or a negative sb200_status; the message is in sb200_last_error().
+ *
+ * Grid convention (reference: include/stencil/boundary_matrix.hpp:54-59,115-123):
+ * row-major, x fastest; every axis carries `radius` halo cells on both sides
+ * which are never written (Dirichlet).  n[0]=x, n[1]=y, n[2]=z interior extents;
+ * unused axes have n = 1 and no halo.
+ */
+#ifndef STENCIL_B200_H
+#define STENCIL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB200_ABI_VERSION 1
+
+typedef enum sb200_status {
+    SB200_OK = 0,
+    SB200_ERR_INVALID = -1,     /* bad descriptor / argument */
+    SB200_ERR_CUDA = -2,        /* a CUDA runtime/driver call failed */
+    SB200_ERR_UNSUPPORTED = -3, /* valid request this backend cannot serve */
+    SB200_ERR_NO_DEVICE = -4    /* no CUDA device: there is NO CPU fallback */
+} sb200_status;
+
+typedef enum sb200_shape { SB200_STAR = 0, SB200_BOX = 1 } sb200_shape;
+typedef enum sb200_dtype { SB200_F32 = 0, SB200_F64 = 1 } sb200_dtype;
+typedef enum sb200_init { SB200_INIT_REF = 0, SB200_INIT_RANDOM = 1 } sb200_init;
+
+/* Kernel family selector (sb200_desc.kernel).  AUTO picks the fastest family
+ * that supports the descriptor; the others force one (tests, experiments). */
+typedef enum sb200_kernel {
+    SB200_KERNEL_AUTO = 0,
+    SB200_KERNEL_GENERIC = 1, /* one step per launch, any ndim/shape/radius   */
+    SB200_KERNEL_WARP2D = 2,  /* 2-D r=1, register/shuffle temporal blocking   */
+    SB200_KERNEL_TMA3D = 3    /* 3-D r=1, TMA-staged z-streaming, temporal blk */
+} sb200_kernel;
+
+/* Problem descriptor.  Replaces the reference's `Arguments{block_size,
+ * iterations, input, output}` (stencil_slave.hpp:13-24) plus the shape data
+ * held inside its BoundaryMatrixView members (boundary_matrix.hpp:221-226). */
+typedef struct sb200_desc {
+    int32_t ndim;        /* 1, 2 or 3 */
+    int32_t shape;       /* sb200_shape */
+    int32_t dtype;       /* sb200_dtype */
+    uint32_t radius;     /* >= 1 */
+    uint64_t n[3];       /* interior extents x,y,z */
+    uint32_t iterations; /* T */
+    uint32_t time_block; /* fused steps per HBM round trip; 0 = auto */
+    uint32_t block_hint; /* reference -b/--block-size; a tuning hint only */
+    int32_t kernel;      /* sb200_kernel */
+} sb200_desc;
+
+/* Timing breakdown of one call (milliseconds; device times from CUDA events). */
+typedef struct sb200_timing {
+    double h2d_ms;
+    double sweep_ms;
+    double d2h_ms;
+    double wall_ms;
+    uint32_t launches;     /* kernels launched by the sweep */
+    uint32_t time_block;   /* fused depth actually used */
+    int32_t kernel;        /* family actually used */
+    int32_t result_in_out; /* 1: step T is in `out`, 0: in `in` (T parity) */
+} sb200_timing;
+
+/* Device-side grid layout chosen by the library for a descriptor: padded so the
+ * first interior x is 128-byte aligned and the row pitch is a multiple of 128 B.
+ * element (x,y,z) in interior coordinates (halo = negative / >= n) lives at
+ *   base + ((z + oz) * pitch_y + (y + oy)) * pitch_x + (x + ox)   [elements]. */
+typedef struct sb200_layout {
+    uint64_t pitch_x;  /* elements per row */
+    uint64_t pitch_y;  /* rows per plane */
+    uint64_t planes;   /* planes allocated (incl. halo / ghost planes) */
+    uint64_t ox, oy, oz;
+    uint64_t bytes;    /* total allocation size */
+} sb200_layout;
+
+/* ---- library ---------------------------------------------------------------- */
+int sb200_abi_version(void);
+const char* sb200_last_error(void);
+/* Number of visible CUDA devices (0 if none / driver missing). */
+int sb200_device_count(void);
+/* Bind the calling process to `device` (one process per GPU). */
+int sb200_init(int device);
+void sb200_finalize(void);
+
+/* ---- the drop-in call -------------------------------------------------------
+ * Host buffers `in`/`out`: padded arrays, (n[a] + 2*radius) per used axis, dense.
+ * Runs T = desc->iterations double-buffered sweeps on the GPU.  On return the
+ * buffer selected by T's parity holds step T (odd: out, even: in), exactly like
+ * the reference kernels that swap their host views every step
+ * (stencil_dma.cpp:556-557; oracle stencil.cpp:129-134).  Blocking. */
+int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* timing);
+
+/* ---- device-resident API (bench, multi-GPU slabs) ----------------------------
+ * `ghost` = extra planes on each side of the outermost axis beyond `radius`
+ * (slab decomposition: ghost planes hold neighbour data).  0 for single GPU. */
+int sb200_layout_for(const sb200_desc* desc, uint32_t ghost, sb200_layout* layout);
+
+/* Sweep `steps` time steps between two device buffers laid out per
+ * sb200_layout_for(desc, ghost).  `lo_is_boundary`/`hi_is_boundary` say whether
+ * the low/high end of the outermost axis is the global Dirichlet halo (1) or a
+ * slab face with `ghost` valid neighbour planes (0).  With ghost planes, at most
+ * ghost/radius steps can be taken before the ghosts must be refreshed; the call
+ * fails with SB200_ERR_INVALID beyond that.  Work is enqueued on `stream`
+ * (a cudaStream_t, or NULL for the legacy default stream) and NOT synchronised.
+ * *result_in_b is set to 1 if the final state is in `b`, 0 if in `a`. */
+int sb200_sweep_device(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
+                       int hi_is_boundary, void* a, void* b, uint32_t steps, void* stream,
+                       int* result_in_b, uint32_t* launches);
+
+/* Same, but restricted to output planes [z_begin, z_end) of the outermost axis
+ * (interior coordinates of this slab).  Used to compute slab faces first and
+ * overlap the halo exchange with the interior.  One fused block of `steps`
+ * (<= max time block) only; a -> b. */
+int sb200_sweep_device_range(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
+                             int hi_is_boundary, const void* a, void* b, uint32_t steps,
+                             uint64_t z_begin, uint64_t z_end, void* stream,
+                             uint32_t* launches);
+
+/* Initialise a device grid (both halo and interior), reference init
+ * (stencil.cpp:190-207: interior 0, x faces 1, other halo 0) or the counter-based
+ * random init.  `z_offset`/`z_total` place a slab inside the global grid so every
+ * slab can be generated independently. */
+int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int init,
+                      uint64_t seed, uint64_t z_offset, uint64_t z_total, void* stream);
+
+/* Copy between a dense host-layout padded array and the device layout. */
+int sb200_upload(const sb200_desc* desc, uint32_t ghost, const void* host, void* dev,
+                 void* stream);
+int sb200_download(const sb200_desc* desc, uint32_t ghost, const void* dev, void* host,
+                   void* stream);
+
+/* Order-independent 64-bit checksum of the interior of a device grid:
+ * sum over points of mix64(bits(value) ^ mix64(global linear index)).
+ * Used for bit-exact 1-vs-N GPU and full-size parity checks.  Blocking. */
+int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* grid,
+                          uint64_t z_offset, uint64_t z_total, void* stream, uint64_t* out);
+
+/* Largest time block the chosen kernel family supports for this descriptor. */
+int sb200_max_time_block(const sb200_desc* desc);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STENCIL_B200_H */

@@ -1,0 +1,112 @@
+// ref_driver.cpp — drives the UNMODIFIED reference Stencil::check_result
+// (/root/reference/src/stencil/stencil.cpp:75-151) to extract the full grid its naive
+// loop produces.  check_result only reports the first element that differs from the
+// accelerator result by >= 1e-4 (stencil.cpp:137-144), so the grid is recovered one
+// element at a time: elements already known are planted in matrix/result, the rest are
+// set far away (1e9), and the hooked printf (hook.h) captures the reference's value of
+// the first unknown element.  O(N^2) sweeps — fine for the small golden grids.
+// Test infrastructure only; built into oracle/_ref/libref.so by oracle/Makefile.
+#include <cstdarg>
+#include <cstdio>
+#include <vector>
+
+#define private public  // reach Stencil::matrix / result / options (stencil.hpp:46-51)
+#include <stencil/stencil.hpp>
+#undef private
+#include "slave/stencil_slave.hpp"
+
+extern "C" {
+void slave_stencil_iterate_dma(Arguments*) {}
+void slave_stencil_iterate_dma_static_unroll(Arguments*) {}
+void slave_stencil_iterate_dma_slave_pack(Arguments*) {}
+void slave_stencil_iterate_rma(Arguments*) {}
+}
+
+namespace {
+thread_local double g_naive = 0.0;
+thread_local unsigned g_row = 0, g_col = 0;
+thread_local bool g_hit = false;
+}  // namespace
+
+namespace std {
+int sb200_ref_capture(const char* fmt, ...) {
+    (void)fmt;
+    va_list ap;
+    va_start(ap, fmt);
+    g_row = va_arg(ap, unsigned);
+    g_col = va_arg(ap, unsigned);
+    g_naive = va_arg(ap, double);
+    va_end(ap);
+    g_hit = true;
+    return 0;
+}
+}  // namespace std
+
+extern "C" {
+// Fills out[N*N] (interior only, row-major) with the reference naive result after T
+// iterations of the radius-r star stencil on its own initial condition. Returns 0, or
+// -1 if the probe protocol broke (should not happen).
+int ref_naive_2d_f32(unsigned N, unsigned r, unsigned T, float* out) {
+    ProgramOptions opts{};
+    opts.matrix_size = N;
+    opts.block_size = N;
+    opts.iterations = T;
+    opts.radius = r;
+    opts.repeat_count = 1;
+    opts.check_result = true;
+    Stencil s(opts);
+    s.initialize_matrix();
+    constexpr float kFar = 1.0e9f;
+    for (unsigned row = 0; row != N; ++row)
+        for (unsigned col = 0; col != N; ++col) {
+            s.matrix.elem_at(row, col) = kFar;
+            s.result.elem_at(row, col) = kFar;
+        }
+    for (unsigned idx = 0; idx != N * N; ++idx) {
+        g_hit = false;
+        bool const ok = s.check_result();
+        if (ok || !g_hit || g_row * N + g_col != idx) return -1;
+        float const v = static_cast<float>(g_naive);
+        out[idx] = v;
+        s.matrix.elem_at(g_row, g_col) = v;
+        s.result.elem_at(g_row, g_col) = v;
+    }
+    return s.check_result() ? 0 : -1;
+}
+
+// The reference's self-check used as a black-box verifier: plant `grid` (interior N*N)
+// as the accelerator result and return check_result() (1 = within 1e-4 everywhere).
+int ref_check_2d_f32(unsigned N, unsigned r, unsigned T, const float* grid) {
+    ProgramOptions opts{};
+    opts.matrix_size = N;
+    opts.block_size = N;
+    opts.iterations = T;
+    opts.radius = r;
+    opts.repeat_count = 1;
+    Stencil s(opts);
+    s.initialize_matrix();
+    for (unsigned row = 0; row != N; ++row)
+        for (unsigned col = 0; col != N; ++col) {
+            s.matrix.elem_at(row, col) = grid[row * N + col];
+            s.result.elem_at(row, col) = grid[row * N + col];
+        }
+    return s.check_result() ? 1 : 0;
+}
+
+// Time the reference's own naive loop (whole check_result: init + sweep + compare), for
+// the "reference"-kind CPU baseline. Returns seconds.
+double ref_time_check_2d_f32(unsigned N, unsigned r, unsigned T) {
+    ProgramOptions opts{};
+    opts.matrix_size = N;
+    opts.block_size = N;
+    opts.iterations = T;
+    opts.radius = r;
+    opts.repeat_count = 1;
+    Stencil s(opts);
+    s.initialize_matrix();
+    auto const t0 = std::chrono::steady_clock::now();
+    (void)s.check_result();
+    auto const t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+}

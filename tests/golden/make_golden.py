@@ -1,0 +1,32 @@
+"""Generate tests/golden/ref_2d_f32.npz from the GENUINE reference naive loop.
+
+Runs only where /root/reference is mounted (the build container): oracle/_ref/libref.so
+is the reference's own src/stencil/stencil.cpp compiled by oracle/Makefile, and
+oracle.ref_naive_2d_f32 recovers the full grid Stencil::check_result computes
+(stencil.cpp:75-131).  The fixture travels to the GPU box; the reference does not.
+
+    python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
+import oracle  # noqa: E402
+
+# (N, radius, T): sizes from the reference's own sweep (run_expr.py:6,14: N = 8*block,
+# block 8 -> N 64) down to tiny/ragged grids; radii the CLI exposes (-r).
+CASES = [
+    (1, 1, 1), (2, 1, 3), (3, 1, 2), (5, 2, 4), (8, 1, 1), (8, 1, 2), (13, 1, 9),
+    (16, 1, 10), (16, 1, 33), (24, 2, 7), (32, 3, 5), (40, 4, 9), (48, 1, 50),
+    (64, 1, 100), (64, 2, 16), (64, 1, 1000),
+]
+
+if __name__ == "__main__":
+    oracle.build()
+    out = {}
+    for N, r, T in CASES:
+        out[f"N{N}_r{r}_T{T}"] = oracle.ref_naive_2d_f32(N, r, T)
+        print(N, r, T, "%.15f" % out[f"N{N}_r{r}_T{T}"][0, 0])
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "ref_2d_f32.npz"), **out)
