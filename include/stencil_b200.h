@@ -35,7 +35,7 @@ typedef enum sb200_status {
 
 typedef enum sb200_shape { SB200_STAR = 0, SB200_BOX = 1 } sb200_shape;
 typedef enum sb200_dtype { SB200_F32 = 0, SB200_F64 = 1 } sb200_dtype;
-typedef enum sb200_init { SB200_INIT_REF = 0, SB200_INIT_RANDOM = 1 } sb200_init;
+typedef enum sb200_init_kind { SB200_INIT_REF = 0, SB200_INIT_RANDOM = 1 } sb200_init_kind;
 
 /* Kernel family selector (sb200_desc.kernel).  AUTO picks the fastest family
  * that supports the descriptor; the others force one (tests, experiments). */
@@ -146,6 +146,10 @@ int sb200_download(const sb200_desc* desc, uint32_t ghost, const void* dev, void
  * Used for bit-exact 1-vs-N GPU and full-size parity checks.  Blocking. */
 int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* grid,
                           uint64_t z_offset, uint64_t z_total, void* stream, uint64_t* out);
+
+/* Pinned host memory for callers that want full-speed PCIe copies in sb200_run_host. */
+int sb200_host_alloc(void** ptr, size_t bytes);
+int sb200_host_free(void* ptr);
 
 /* Largest time block the chosen kernel family supports for this descriptor. */
 int sb200_max_time_block(const sb200_desc* desc);

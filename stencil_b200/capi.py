@@ -1,0 +1,120 @@
+"""ctypes binding of the C ABI in include/stencil_b200.h (libstencil_b200.so).
+
+This is the Python-side stub a maintainer would use to reach the same entry points the
+C++ host (stencil_b200/host/) calls; tests and bench.py go through it.  There is NO
+fallback: if the shared library is missing or no GPU is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libstencil_b200.so")
+
+STAR, BOX = 0, 1
+F32, F64 = 0, 1
+INIT_REF, INIT_RANDOM = 0, 1
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_WARP2D, KERNEL_TMA3D = 0, 1, 2, 3
+OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE = 0, -1, -2, -3, -4
+
+# every symbol include/stencil_b200.h declares
+SYMBOLS = [
+    "sb200_abi_version", "sb200_last_error", "sb200_device_count", "sb200_init",
+    "sb200_finalize", "sb200_run_host", "sb200_layout_for", "sb200_sweep_device",
+    "sb200_sweep_device_range", "sb200_fill_device", "sb200_upload", "sb200_download",
+    "sb200_checksum_device", "sb200_host_alloc", "sb200_host_free", "sb200_max_time_block",
+]
+
+
+class Desc(ctypes.Structure):
+    _fields_ = [
+        ("ndim", ctypes.c_int32), ("shape", ctypes.c_int32), ("dtype", ctypes.c_int32),
+        ("radius", ctypes.c_uint32), ("n", ctypes.c_uint64 * 3),
+        ("iterations", ctypes.c_uint32), ("time_block", ctypes.c_uint32),
+        ("block_hint", ctypes.c_uint32), ("kernel", ctypes.c_int32),
+    ]
+
+
+class Timing(ctypes.Structure):
+    _fields_ = [
+        ("h2d_ms", ctypes.c_double), ("sweep_ms", ctypes.c_double), ("d2h_ms", ctypes.c_double),
+        ("wall_ms", ctypes.c_double), ("launches", ctypes.c_uint32),
+        ("time_block", ctypes.c_uint32), ("kernel", ctypes.c_int32),
+        ("result_in_out", ctypes.c_int32),
+    ]
+
+
+class Layout(ctypes.Structure):
+    _fields_ = [
+        ("pitch_x", ctypes.c_uint64), ("pitch_y", ctypes.c_uint64), ("planes", ctypes.c_uint64),
+        ("ox", ctypes.c_uint64), ("oy", ctypes.c_uint64), ("oz", ctypes.c_uint64),
+        ("bytes", ctypes.c_uint64),
+    ]
+
+
+class StencilError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"stencil_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Load libstencil_b200.so (fails loudly if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build the CUDA extension first "
+                "(python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        vp, u32, u64, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_int
+        dp = ctypes.POINTER(Desc)
+        L.sb200_abi_version.restype = i32
+        L.sb200_last_error.restype = ctypes.c_char_p
+        L.sb200_device_count.restype = i32
+        L.sb200_init.argtypes = [i32]
+        L.sb200_finalize.restype = None
+        L.sb200_run_host.argtypes = [dp, vp, vp, ctypes.POINTER(Timing)]
+        L.sb200_layout_for.argtypes = [dp, u32, ctypes.POINTER(Layout)]
+        L.sb200_sweep_device.argtypes = [dp, u32, i32, i32, vp, vp, u32, vp,
+                                         ctypes.POINTER(i32), ctypes.POINTER(u32)]
+        L.sb200_sweep_device_range.argtypes = [dp, u32, i32, i32, vp, vp, u32, u64, u64, vp,
+                                               ctypes.POINTER(u32)]
+        L.sb200_fill_device.argtypes = [dp, u32, vp, i32, u64, u64, u64, vp]
+        L.sb200_upload.argtypes = [dp, u32, vp, vp, vp]
+        L.sb200_download.argtypes = [dp, u32, vp, vp, vp]
+        L.sb200_checksum_device.argtypes = [dp, u32, vp, u64, u64, vp, ctypes.POINTER(u64)]
+        L.sb200_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
+        L.sb200_host_free.argtypes = [vp]
+        L.sb200_max_time_block.argtypes = [dp]
+        _lib = L
+    return _lib
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        raise StencilError(rc, lib().sb200_last_error().decode())
+    return rc
+
+
+def make_desc(n, radius=1, shape=STAR, dtype=F32, iterations=1, time_block=0, block_hint=0,
+              kernel=KERNEL_AUTO) -> Desc:
+    """n = (nx,), (nx, ny) or (nx, ny, nz) interior extents, x fastest."""
+    n = tuple(int(v) for v in n)
+    d = Desc()
+    d.ndim = len(n)
+    d.shape, d.dtype, d.radius = shape, dtype, radius
+    for a in range(3):
+        d.n[a] = n[a] if a < len(n) else 1
+    d.iterations, d.time_block, d.block_hint, d.kernel = iterations, time_block, block_hint, kernel
+    return d
+
+
+def layout_for(desc: Desc, ghost: int = 0) -> Layout:
+    lay = Layout()
+    check(lib().sb200_layout_for(ctypes.byref(desc), ghost, ctypes.byref(lay)))
+    return lay

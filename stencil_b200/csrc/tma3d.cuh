@@ -1,0 +1,280 @@
+// tma3d.cuh — 3-D radius-1 star (7-point) sweep, K time steps fused per HBM round trip.
+//
+// B200 design: a CTA owns an xy tile (32*PXV x 64 points incl. a K-deep halo) and
+// streams along z, the slowest axis.  Level-0 planes are staged into a shared-memory
+// ring by TMA (cp.async.bulk.tensor.3d + mbarrier expect-tx — the sm_100a counterpart
+// of the reference's athread_dma_iget + reply counter, stencil_dma.cpp:236-247,448),
+// out-of-range box parts are zero-filled by the TMA unit so loads need no bounds
+// code.  Each thread owns PXV consecutive x (one 128-bit shared load) by 4 rows;
+// x-neighbours come from adjacent lanes by warp shuffle (a warp spans the tile's full
+// x extent), y-neighbours from shared memory, and the z-1 / z+1 planes are folded into
+// per-thread register partial sums, so every plane of every time level is read from
+// shared memory exactly once.  Time levels 1..K-1 ping-pong through double-buffered
+// shared planes: ONE __syncthreads per streamed plane regardless of K.  The final level
+// is stored straight from registers with 128-bit coalesced stores.
+//
+// Per-point order is the oracle's (generalising reference
+// stencil.cpp:103-125):  ((((((0+xl)+xr)+yl)+yr)+zl)+zr) * avg, hence bit-identical for
+// any K.  Points outside the update domain pass through unchanged at every level.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace sb200 {
+
+template <class T, int K> struct T3 {
+    static constexpr int PXV = 16 / (int)sizeof(T);  // x points per thread (128-bit)
+    static constexpr int PY = 4;                     // rows per thread
+    static constexpr int TXN = 32, TYN = 16;
+    static constexpr int THREADS = TXN * TYN;
+    static constexpr int BX = TXN * PXV, BY = TYN * PY;
+    static constexpr int HLX = (K + PXV - 1) / PXV * PXV;
+    static constexpr int VX = (BX - HLX - K) / PXV * PXV;
+    static constexpr int VY = BY - 2 * K;
+    static constexpr int STAGES = K <= 2 ? 4 : 3;
+    static constexpr int PLANE = BX * BY;  // elements
+    static constexpr size_t PLANE_BYTES = (size_t)PLANE * sizeof(T);
+    static constexpr size_t SMEM = PLANE_BYTES * (STAGES + 2 * (K - 1)) + 8 * STAGES + 128;
+};
+constexpr int T3_MAXK = 3;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar,
+                                            int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+template <class T, int N> struct VecN;
+template <> struct VecN<float, 4> {
+    static __device__ __forceinline__ void ld(const float* p, float* v) {
+        const float4 f = *reinterpret_cast<const float4*>(p);
+        v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+    }
+    static __device__ __forceinline__ void st(float* p, const float* v) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+};
+template <> struct VecN<double, 2> {
+    static __device__ __forceinline__ void ld(const double* p, double* v) {
+        const double2 f = *reinterpret_cast<const double2*>(p);
+        v[0] = f.x; v[1] = f.y;
+    }
+    static __device__ __forceinline__ void st(double* p, const double* v) {
+        *reinterpret_cast<double2*>(p) = make_double2(v[0], v[1]);
+    }
+};
+
+// Per-thread state of one time level: PY rows x PXV points.
+template <class T, int PXV, int PY> struct T3Level {
+    T t[PY][PXV];    // (in-plane partial of plane a-1) + centre of plane a-2
+    T cm1[PY][PXV];  // centre of plane a-1 (also its pass-through value)
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int i = 0; i < PY; ++i)
+#pragma unroll
+            for (int k = 0; k < PXV; ++k) t[i][k] = cm1[i][k] = T(0);
+    }
+};
+
+// Plane `src` (dense BY x BX in shared memory) of level l-1 arrives; emit the finished
+// plane a-1 of level l into o[][] (registers).
+template <class T, int K>
+__device__ __forceinline__ void t3_level_step(const T* __restrict__ src,
+                                              T3Level<T, T3<T, K>::PXV, T3<T, K>::PY>& L,
+                                              int tx, int ty, T avg, const bool (&mxy)[4][T3<T, K>::PXV],
+                                              bool plane_upd, T (&o)[4][T3<T, K>::PXV]) {
+    using C = T3<T, K>;
+    constexpr int PXV = C::PXV, PY = C::PY;
+    const int lx = tx * PXV, ly = ty * PY;
+    T c[PY + 2][PXV];  // rows ly-1 .. ly+PY (clamped at the tile edge: halo shrink)
+    const int r_up = ly > 0 ? ly - 1 : 0;
+    const int r_dn = ly + PY < C::BY ? ly + PY : C::BY - 1;
+    VecN<T, PXV>::ld(src + r_up * C::BX + lx, c[0]);
+#pragma unroll
+    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + (ly + i) * C::BX + lx, c[i + 1]);
+    VecN<T, PXV>::ld(src + r_dn * C::BX + lx, c[PY + 1]);
+#pragma unroll
+    for (int i = 0; i < PY; ++i) {
+        const T lft = __shfl_up_sync(0xffffffffu, c[i + 1][PXV - 1], 1);
+        const T rgt = __shfl_down_sync(0xffffffffu, c[i + 1][0], 1);
+#pragma unroll
+        for (int k = 0; k < PXV; ++k) {
+            const T xl = k == 0 ? lft : c[i + 1][k - 1];
+            const T xr = k == PXV - 1 ? rgt : c[i + 1][k + 1];
+            const T s = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), c[i][k]), c[i + 2][k]);
+            const T f = mul_rn(add_rn(L.t[i][k], c[i + 1][k]), avg);
+            o[i][k] = (plane_upd && mxy[i][k]) ? f : L.cm1[i][k];
+            L.t[i][k] = add_rn(s, L.cm1[i][k]);
+            L.cm1[i][k] = c[i + 1][k];
+        }
+    }
+}
+
+template <class T, int K>
+__global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
+sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out, Grid g,
+                   Domain dom, long long ob, long long oe, int ntx, int nty, int chunk_planes,
+                   T avg) {
+    using C = T3<T, K>;
+    constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // 128-byte align the TMA destinations
+    unsigned char* base = smem_raw + ((128 - (smem_u32(smem_raw) & 127)) & 127);
+    T* ring = reinterpret_cast<T*>(base);
+    T* lbuf = ring + (size_t)S * C::PLANE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lbuf + (size_t)2 * (K - 1) * C::PLANE);
+
+    const int tid = threadIdx.x;
+    const int tx = tid & 31, ty = tid >> 5;
+    const int b = blockIdx.x;
+    const int tix = b % ntx, tiy = (b / ntx) % nty;
+    const long long chunk = b / (ntx * nty);
+    const long long zb = ob + chunk * chunk_planes;
+    const long long ze = zb + chunk_planes < oe ? zb + chunk_planes : oe;
+    const long long gx0 = (long long)tix * C::VX - C::HLX;  // interior coords of tile (0,0)
+    const long long gy0 = (long long)tiy * C::VY - K;
+    const long long z_first = zb - K;
+    const int nin = (int)(ze - zb) + 2 * K;  // level-0 planes streamed
+    const int nsteps = nin + K - 1;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int cx = (int)(gx0 + g.ox), cy = (int)(gy0 + g.oy);
+    const long long cz0 = z_first + g.oz;
+    if (tid == 0) {
+        for (int s = 0; s < S && s < nin; ++s) {
+            mbar_expect_tx(&bars[s], (uint32_t)C::PLANE_BYTES);
+            tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, (int)(cz0 + s));
+        }
+    }
+
+    // per-point update masks in x/y and store validity
+    bool mxy[PY][PXV];
+    bool row_ok[PY];
+    const long long gx = gx0 + tx * PXV, gy = gy0 + ty * PY;
+#pragma unroll
+    for (int i = 0; i < PY; ++i) {
+        const bool yin = gy + i >= 0 && gy + i < g.n[1];
+        row_ok[i] = yin && ty * PY + i >= K && ty * PY + i < K + C::VY;
+#pragma unroll
+        for (int k = 0; k < PXV; ++k) mxy[i][k] = yin && gx + k >= 0 && gx + k < g.n[0];
+    }
+    const bool col_ok = tx * PXV >= C::HLX && tx * PXV < C::HLX + C::VX && gx < g.n[0];
+    const bool col_full = gx + PXV <= g.n[0];
+
+    T3Level<T, PXV, PY> lv[K];
+#pragma unroll
+    for (int l = 0; l < K; ++l) lv[l].init();
+
+    T* __restrict__ dst = out + g.idx(gx, gy, 0);
+    const long long plane_stride = g.pitch_x * g.pitch_y;
+
+    for (int j = 0; j < nsteps; ++j) {
+        const int st = j % S;
+        if (j < nin) mbar_wait(&bars[st], (uint32_t)((j / S) & 1));
+#pragma unroll
+        for (int l = 0; l < K; ++l) {
+            // level l+1 is active on steps [l, nin + l)
+            if (j >= l && j < nin + l) {
+                const T* src = l == 0 ? ring + (size_t)st * C::PLANE
+                                      : lbuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::PLANE;
+                const long long zo = z_first + (j - 2 * l) - 1;  // plane being emitted
+                const bool upd = zo >= dom.lo && zo < dom.hi;
+                T o[PY][PXV];
+                t3_level_step<T, K>(src, lv[l], tx, ty, avg, mxy, upd, o);
+                if (l < K - 1) {
+                    T* wb = lbuf + (size_t)(2 * l + (j & 1)) * C::PLANE;
+#pragma unroll
+                    for (int i = 0; i < PY; ++i)
+                        VecN<T, PXV>::st(wb + (ty * PY + i) * C::BX + tx * PXV, o[i]);
+                } else if (col_ok && zo >= zb && zo < ze) {
+                    T* p = dst + zo * plane_stride;
+#pragma unroll
+                    for (int i = 0; i < PY; ++i) {
+                        if (row_ok[i]) {
+                            if (col_full) {
+                                VecN<T, PXV>::st(p + i * g.pitch_x, o[i]);
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < PXV; ++k)
+                                    if (gx + k < g.n[0]) p[i * g.pitch_x + k] = o[i][k];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0 && j + S < nin) {
+            mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
+            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy,
+                        (int)(cz0 + j + S));
+        }
+    }
+}
+
+struct T3Plan {
+    int ntx, nty, chunk_planes;
+    long long nchunks, blocks;
+};
+
+template <class T, int K>
+static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count) {
+    using C = T3<T, K>;
+    T3Plan p;
+    p.ntx = (int)((nx + C::VX - 1) / C::VX);
+    p.nty = (int)((ny + C::VY - 1) / C::VY);
+    const long long tiles = (long long)p.ntx * p.nty;
+    // pick the chunk count maximising (useful planes / streamed planes) x (wave fill)
+    double best = -1.0;
+    long long best_c = 1;
+    for (long long c = 1; c <= 256 && c <= planes; ++c) {
+        const long long cp = (planes + c - 1) / c;
+        const long long nc = (planes + cp - 1) / cp;
+        const long long blocks = tiles * nc;
+        const long long waves = (blocks + sm_count - 1) / sm_count;
+        const double fill = (double)blocks / (double)(waves * sm_count);
+        const double eff = fill * (double)cp / (double)(cp + 3 * K - 1);
+        if (eff > best + 1e-9) {
+            best = eff;
+            best_c = nc;
+            p.chunk_planes = (int)cp;
+        }
+    }
+    p.nchunks = best_c;
+    p.blocks = tiles * p.nchunks;
+    return p;
+}
+
+}  // namespace sb200

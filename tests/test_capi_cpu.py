@@ -1,0 +1,71 @@
+"""CPU tests of the C-ABI boundary: the library loads, exports every symbol
+include/stencil_b200.h declares, validates descriptors, and FAILS LOUDLY without a GPU
+(no compute is attempted here)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from stencil_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_all_exported(built):
+    hdr = open(os.path.join(ROOT, "include", "stencil_b200.h")).read()
+    declared = set(re.findall(r"\b(sb200_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(capi.SYMBOLS)
+    L = capi.lib()
+    for s in declared:
+        assert getattr(L, s) is not None
+    assert L.sb200_abi_version() == 1
+
+
+def test_struct_sizes_match_header(built):
+    assert ctypes.sizeof(capi.Desc) == 56
+    assert ctypes.sizeof(capi.Timing) == 48
+    assert ctypes.sizeof(capi.Layout) == 56
+
+
+def test_layout_is_aligned(built):
+    for dtype, es in ((capi.F32, 4), (capi.F64, 8)):
+        for n in ((5,), (100, 7), (512, 512, 512), (1023, 3, 2)):
+            lay = capi.layout_for(capi.make_desc(n, dtype=dtype), 0)
+            assert (lay.ox * es) % 128 == 0 and (lay.pitch_x * es) % 128 == 0
+            assert lay.pitch_x >= lay.ox + n[0] + 1
+            assert lay.bytes == lay.pitch_x * lay.pitch_y * lay.planes * es
+    lay = capi.layout_for(capi.make_desc((8, 8, 8)), ghost=3)
+    assert lay.planes == 8 + 2 * (1 + 3) and lay.oz == 4
+
+
+@pytest.mark.parametrize("kw", [dict(n=(0, 4)), dict(n=(4, 4), radius=0), dict(n=(4, 4), radius=17),
+                                dict(n=(4, 4), shape=7), dict(n=(4, 4), dtype=5)])
+def test_invalid_descriptors_rejected(built, kw):
+    d = capi.make_desc(**kw)
+    lay = capi.Layout()
+    assert capi.lib().sb200_layout_for(ctypes.byref(d), 0, ctypes.byref(lay)) == capi.ERR_INVALID
+    assert capi.lib().sb200_last_error()
+
+
+def test_no_gpu_means_loud_failure(built):
+    L = capi.lib()
+    if L.sb200_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    a = np.zeros((6, 6), np.float32)
+    b = np.zeros((6, 6), np.float32)
+    d = capi.make_desc((4, 4))
+    rc = L.sb200_run_host(ctypes.byref(d), a.ctypes.data, b.ctypes.data, None)
+    assert rc == capi.ERR_NO_DEVICE
+    assert b"no CPU fallback" in L.sb200_last_error()
+    with pytest.raises(capi.StencilError):
+        capi.check(rc)
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "stencil_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "liboracle" not in src, f

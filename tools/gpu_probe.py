@@ -1,0 +1,63 @@
+"""Developer timing probe (run under gpurun): device-resident sweeps of each BASELINE
+config with several kernels / time blocks, CUDA-event timed.  Prints one line per variant.
+Not the bench (bench.py is); used to choose defaults."""
+import ctypes
+import sys
+import os
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from stencil_b200 import capi, sweep
+
+capi.check(capi.lib().sb200_init(0))
+PEAK = 6529.1
+
+
+def run(name, n, shape, dtype, T, kernel, k, reps=3):
+    d = capi.make_desc(n, 1, shape, dtype, T, time_block=k, kernel=kernel)
+    try:
+        g = sweep.DeviceGrids(d)
+        g.fill(capi.INIT_RANDOM, seed=1)
+        g.sweep(min(T, 2 * max(k, 1)))
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            nl = g.sweep(T)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        pts = 1
+        for v in n:
+            pts *= v
+        gs = pts * T / best / 1e6
+        es = 8 if dtype == capi.F64 else 4
+        print(f"{name:10s} n={n} kern={kernel} k={k} T={T}: {best:9.3f} ms  {gs:9.1f} GStencil/s  "
+              f"alg {gs * 2 * es:8.1f} GB/s  frac {gs * 2 * es / PEAK:5.3f}  launches {nl}", flush=True)
+        del g
+    except Exception as e:  # noqa: BLE001
+        print(f"{name} n={n} kern={kernel} k={k}: FAILED {e}", flush=True)
+    torch.cuda.empty_cache()
+
+
+which = sys.argv[1:] or ["c1", "c2", "c3", "c4"]
+if "c2" in which:
+    for k in (1, 2, 3):
+        run("c2-7pt", (512, 512, 512), capi.STAR, capi.F64, 24, capi.KERNEL_TMA3D, k)
+    run("c2-7pt", (512, 512, 512), capi.STAR, capi.F64, 10, capi.KERNEL_GENERIC, 1)
+    for k in (1, 2, 3):
+        run("c2-7pt-f32", (512, 512, 512), capi.STAR, capi.F32, 24, capi.KERNEL_TMA3D, k)
+if "c1" in which:
+    for k in (1, 2, 4, 6, 8):
+        run("c1-5pt-f64", (4096, 4096), capi.STAR, capi.F64, 96, capi.KERNEL_WARP2D, k)
+    run("c1-5pt-f64", (4096, 4096), capi.STAR, capi.F64, 20, capi.KERNEL_GENERIC, 1)
+    for k in (1, 4, 8):
+        run("c1-5pt-f32", (4096, 4096), capi.STAR, capi.F32, 96, capi.KERNEL_WARP2D, k)
+if "c4" in which:
+    for k in (1, 2, 4, 6, 8):
+        run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k)
+    run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 6, capi.KERNEL_GENERIC, 1)
+if "c3" in which:
+    run("c3-27pt", (512, 512, 512), capi.BOX, capi.F64, 6, capi.KERNEL_GENERIC, 1)
