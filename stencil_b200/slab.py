@@ -1,0 +1,215 @@
+"""Slab decomposition along the outermost axis, one process per GPU.
+
+The reference decomposes its grid over an 8x8 core mesh and exchanges halos every step
+(block_subview, boundary_matrix.hpp:190-218; RMA puts, stencil_rma.cpp:198-255).  Here
+rank g owns a contiguous slab of planes plus `ghost = radius * k` ghost planes per
+internal face, exchanged once per fused block of k time steps:
+
+    faces first (side stream)  ->  send/recv face planes (NCCL, NVLink)   \
+    interior planes (main stream, concurrently)                             -> join
+
+Per-point arithmetic is the single-GPU kernel's, so results are bitwise independent of
+the number of ranks.  The compute engine is pluggable so the partition / exchange logic
+is unit-tested on CPU with gloo (tests/test_slab_gloo.py injects a CPU engine); the
+product engine is CudaEngine below and nothing else.
+"""
+from __future__ import annotations
+
+import ctypes
+
+from . import capi
+
+_KERNEL_NAMES = {capi.KERNEL_GENERIC: "generic", capi.KERNEL_WARP2D: "warp2d",
+                 capi.KERNEL_TMA3D: "tma3d"}
+
+
+def resolve_kernel(desc: capi.Desc):
+    """(family, fused depth) the library will use for this descriptor (mirrors choose()
+    in csrc/capi.cu; max depth is asked from the library)."""
+    w2d = desc.ndim == 2 and desc.radius == 1
+    t3 = desc.ndim == 3 and desc.radius == 1 and desc.shape == capi.STAR
+    kern = desc.kernel
+    if kern == capi.KERNEL_AUTO:
+        kern = capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3 else capi.KERNEL_GENERIC
+    max_k = {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 8, capi.KERNEL_TMA3D: 3}[kern]
+    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 4, capi.KERNEL_TMA3D: 2}[kern]
+    return kern, min(k, max_k)
+
+
+class CudaEngine:
+    """Device buffers + kernels through the C ABI (the product path)."""
+
+    def __init__(self, desc: capi.Desc, ghost: int, device_index: int):
+        import torch
+        self.torch = torch
+        self.desc, self.ghost = desc, ghost
+        self.device = torch.device("cuda", device_index)
+        self.lay = capi.layout_for(desc, ghost)
+        self.np_dtype = torch.float64 if desc.dtype == capi.F64 else torch.float32
+        es = 8 if desc.dtype == capi.F64 else 4
+        self.raw = [torch.zeros(self.lay.bytes, dtype=torch.uint8, device=self.device) for _ in range(2)]
+        if desc.ndim == 3:
+            shp = (self.lay.planes, self.lay.pitch_y, self.lay.pitch_x)
+            self.off = int(self.lay.oz)
+        else:
+            shp = (self.lay.pitch_y, self.lay.pitch_x)
+            self.off = int(self.lay.oy)
+        self.view = [r.view(self.np_dtype).view(shp) for r in self.raw]
+        assert es * self.view[0].numel() == self.lay.bytes
+        self.side = torch.cuda.Stream(self.device, priority=-1)
+
+    def planes(self, which: int, z0: int, z1: int):
+        return self.view[which][z0 + self.off:z1 + self.off]
+
+    def _st(self, stream=None):
+        s = stream if stream is not None else self.torch.cuda.current_stream(self.device)
+        return ctypes.c_void_p(s.cuda_stream)
+
+    def fill(self, which, init, seed, z_offset, z_total):
+        capi.check(capi.lib().sb200_fill_device(ctypes.byref(self.desc), self.ghost,
+                                                self.raw[which].data_ptr(), init, seed, z_offset,
+                                                z_total, self._st()))
+
+    def sweep_range(self, src, dst, steps, zb, ze, lo_b, hi_b, stream=None) -> int:
+        nl = ctypes.c_uint32(0)
+        capi.check(capi.lib().sb200_sweep_device_range(
+            ctypes.byref(self.desc), self.ghost, lo_b, hi_b, self.raw[src].data_ptr(),
+            self.raw[dst].data_ptr(), steps, zb, ze, self._st(stream), ctypes.byref(nl)))
+        return nl.value
+
+    def sweep_all(self, src, dst, steps) -> tuple[int, int]:
+        in_b, nl = ctypes.c_int(0), ctypes.c_uint32(0)
+        capi.check(capi.lib().sb200_sweep_device(
+            ctypes.byref(self.desc), 0, 1, 1, self.raw[src].data_ptr(), self.raw[dst].data_ptr(),
+            steps, self._st(), ctypes.byref(in_b), ctypes.byref(nl)))
+        return (dst if in_b.value else src), nl.value
+
+    def checksum(self, which, z_offset, z_total) -> int:
+        out = ctypes.c_uint64(0)
+        capi.check(capi.lib().sb200_checksum_device(
+            ctypes.byref(self.desc), self.ghost, self.raw[which].data_ptr(), z_offset, z_total,
+            self._st(), ctypes.byref(out)))
+        return out.value
+
+    # stream plumbing used by SlabSweep
+    def side_stream(self):
+        return self.side
+
+    def fork(self, stream):
+        stream.wait_stream(self.torch.cuda.current_stream(self.device))
+
+    def join(self, stream):
+        self.torch.cuda.current_stream(self.device).wait_stream(stream)
+
+    def stream_ctx(self, stream):
+        return self.torch.cuda.stream(stream)
+
+
+class SlabSweep:
+    """T double-buffered steps of `desc` (the per-rank slab) across `world` ranks."""
+
+    def __init__(self, desc: capi.Desc, rank: int = 0, world: int = 1, engine_factory=None,
+                 dist=None):
+        self.desc, self.rank, self.world = desc, rank, world
+        self.kernel, self.time_block = resolve_kernel(desc)
+        self.kernel_name = _KERNEL_NAMES[self.kernel]
+        self.r = int(desc.radius)
+        self.n_outer = int(desc.n[desc.ndim - 1])
+        if world > 1 and desc.ndim == 1:
+            raise ValueError("1-D grids are not slab-decomposed")
+        self.ghost = self.r * self.time_block if world > 1 else 0
+        if world > 1 and self.n_outer < 2 * self.ghost:
+            raise ValueError(f"slab of {self.n_outer} planes is thinner than two ghost zones "
+                             f"({self.ghost} each); use fewer ranks or a smaller time block")
+        factory = engine_factory or (lambda d, g: CudaEngine(d, g, _current_device()))
+        self.eng = factory(desc, self.ghost)
+        self.cur = 0
+        self.lo_b = 1 if rank == 0 else 0
+        self.hi_b = 1 if rank == world - 1 else 0
+        self.kernels_per_launch_unit = 1 if world == 1 else (1 + (not self.lo_b) + (not self.hi_b))
+        if world > 1:
+            if dist is None:
+                import torch.distributed as dist  # noqa: PLC0415
+            self.dist = dist
+
+    # -- setup ----------------------------------------------------------------------
+    def fill(self, init=capi.INIT_REF, seed=0):
+        off, tot = self.rank * self.n_outer, self.n_outer * self.world
+        if self.world == 1:
+            off = tot = 0
+        self.eng.fill(0, init, seed, off, tot)
+        self.eng.fill(1, capi.INIT_REF, 0, off, tot)
+        self.cur = 0
+
+    def checksum(self) -> int:
+        off, tot = self.rank * self.n_outer, self.n_outer * self.world
+        if self.world == 1:
+            off = tot = 0
+        return self.eng.checksum(self.cur, off, tot)
+
+    def download_initial_into(self, ha, hb, seed):
+        """Fill two host arrays (dense padded layout of ONE rank-local grid) with the same
+        synthetic initial condition, generated on the device (bench e2e leg)."""
+        import numpy as np  # noqa: PLC0415
+        from . import sweep  # noqa: PLC0415
+        g = sweep.DeviceGrids(self.desc, 0)
+        g.fill(capi.INIT_RANDOM, seed)
+        for which, h in ((0, ha), (1, hb)):
+            capi.check(capi.lib().sb200_download(ctypes.byref(self.desc), 0,
+                                                 (g.a, g.b)[which].data_ptr(), h.ctypes.data,
+                                                 g._stream()))
+        g.torch.cuda.synchronize()
+        assert isinstance(ha, np.ndarray)
+
+    # -- the sweep --------------------------------------------------------------------
+    def sweep(self, steps: int) -> int:
+        """Advance `steps` time steps; returns the number of kernels launched."""
+        if self.world == 1:
+            self.cur, nl = self.eng.sweep_all(self.cur, self.cur ^ 1, steps)
+            return nl
+        launches, done = 0, 0
+        while done < steps:
+            k = min(self.time_block, steps - done)
+            launches += self._block(k)
+            done += k
+        return launches
+
+    def _block(self, k: int) -> int:
+        # faces are always `ghost` deep (also for a shorter remainder block) so that every
+        # ghost plane is refreshed to the new time level by each exchange
+        eng, n, g = self.eng, self.n_outer, self.ghost
+        src, dst = self.cur, self.cur ^ 1
+        side = eng.side_stream()
+        nl = 0
+        # 1. faces on the side stream (they gate the exchange)
+        eng.fork(side)
+        with eng.stream_ctx(side):
+            if not self.lo_b:
+                nl += eng.sweep_range(src, dst, k, 0, g, self.lo_b, self.hi_b, side)
+            if not self.hi_b:
+                nl += eng.sweep_range(src, dst, k, n - g, n, self.lo_b, self.hi_b, side)
+        # 2. interior on the main stream, concurrently
+        zb = 0 if self.lo_b else g
+        ze = n if self.hi_b else n - g
+        nl += eng.sweep_range(src, dst, k, zb, ze, self.lo_b, self.hi_b)
+        # 3. exchange the freshly computed face planes into the neighbours' ghost planes
+        with eng.stream_ctx(side):
+            ops = []
+            P2P = self.dist.P2POp
+            if not self.lo_b:
+                ops.append(P2P(self.dist.isend, eng.planes(dst, 0, g), self.rank - 1))
+                ops.append(P2P(self.dist.irecv, eng.planes(dst, -g, 0), self.rank - 1))
+            if not self.hi_b:
+                ops.append(P2P(self.dist.isend, eng.planes(dst, n - g, n), self.rank + 1))
+                ops.append(P2P(self.dist.irecv, eng.planes(dst, n, n + g), self.rank + 1))
+            for w in self.dist.batch_isend_irecv(ops):
+                w.wait()
+        # 4. join
+        eng.join(side)
+        self.cur = dst
+        return nl
+
+
+def _current_device() -> int:
+    import torch  # noqa: PLC0415
+    return torch.cuda.current_device()
