@@ -104,23 +104,21 @@ template <class T, int PXV, int PY> struct T3Level {
     }
 };
 
-// Plane `src` (dense BY x BX in shared memory) of level l-1 arrives; emit the finished
-// plane a-1 of level l into o[][] (registers).
-template <class T, int K>
-__device__ __forceinline__ void t3_level_step(const T* __restrict__ src,
-                                              T3Level<T, T3<T, K>::PXV, T3<T, K>::PY>& L,
-                                              int tx, int ty, T avg, const bool (&mxy)[4][T3<T, K>::PXV],
-                                              bool plane_upd, T (&o)[4][T3<T, K>::PXV]) {
+// Plane of level l-1 arrives (`s` = this thread's base pointer into the dense BY x BX
+// shared plane: row ly, column lx); emit the finished plane a-1 of level l into o[][].
+// FAST: every point this warp owns is updatable in x/y and the emitted plane is inside
+// the update domain, so no pass-through selects are needed (warp-uniform choice).
+template <class T, int K, bool FAST>
+__device__ __forceinline__ void t3_level_step(const T* __restrict__ s, int up_off, int dn_off,
+                                              T3Level<T, T3<T, K>::PXV, T3<T, K>::PY>& L, T avg,
+                                              unsigned mask, T (&o)[4][T3<T, K>::PXV]) {
     using C = T3<T, K>;
     constexpr int PXV = C::PXV, PY = C::PY;
-    const int lx = tx * PXV, ly = ty * PY;
     T c[PY + 2][PXV];  // rows ly-1 .. ly+PY (clamped at the tile edge: halo shrink)
-    const int r_up = ly > 0 ? ly - 1 : 0;
-    const int r_dn = ly + PY < C::BY ? ly + PY : C::BY - 1;
-    VecN<T, PXV>::ld(src + r_up * C::BX + lx, c[0]);
+    VecN<T, PXV>::ld(s + up_off, c[0]);
 #pragma unroll
-    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + (ly + i) * C::BX + lx, c[i + 1]);
-    VecN<T, PXV>::ld(src + r_dn * C::BX + lx, c[PY + 1]);
+    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(s + i * C::BX, c[i + 1]);
+    VecN<T, PXV>::ld(s + dn_off, c[PY + 1]);
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
         const T lft = __shfl_up_sync(0xffffffffu, c[i + 1][PXV - 1], 1);
@@ -129,10 +127,14 @@ __device__ __forceinline__ void t3_level_step(const T* __restrict__ src,
         for (int k = 0; k < PXV; ++k) {
             const T xl = k == 0 ? lft : c[i + 1][k - 1];
             const T xr = k == PXV - 1 ? rgt : c[i + 1][k + 1];
-            const T s = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), c[i][k]), c[i + 2][k]);
+            const T sum = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), c[i][k]), c[i + 2][k]);
             const T f = mul_rn(add_rn(L.t[i][k], c[i + 1][k]), avg);
-            o[i][k] = (plane_upd && mxy[i][k]) ? f : L.cm1[i][k];
-            L.t[i][k] = add_rn(s, L.cm1[i][k]);
+            if (FAST) {
+                o[i][k] = f;
+            } else {
+                o[i][k] = ((mask >> (i * PXV + k)) & 1u) ? f : L.cm1[i][k];
+            }
+            L.t[i][k] = add_rn(sum, L.cm1[i][k]);
             L.cm1[i][k] = c[i + 1][k];
         }
     }
@@ -171,75 +173,96 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     }
     __syncthreads();
     const int cx = (int)(gx0 + g.ox), cy = (int)(gy0 + g.oy);
-    const long long cz0 = z_first + g.oz;
+    const int cz0 = (int)(z_first + g.oz);
     if (tid == 0) {
         for (int s = 0; s < S && s < nin; ++s) {
             mbar_expect_tx(&bars[s], (uint32_t)C::PLANE_BYTES);
-            tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, (int)(cz0 + s));
+            tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, cz0 + s);
         }
     }
 
-    // per-point update masks in x/y and store validity
-    bool mxy[PY][PXV];
-    bool row_ok[PY];
-    const long long gx = gx0 + tx * PXV, gy = gy0 + ty * PY;
+    // per-thread constants: update mask in x/y, store validity, shared-memory offsets
+    const int lx = tx * PXV, ly = ty * PY;
+    const long long gx = gx0 + lx, gy = gy0 + ly;
+    unsigned mask = 0, rows_ok = 0;
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
         const bool yin = gy + i >= 0 && gy + i < g.n[1];
-        row_ok[i] = yin && ty * PY + i >= K && ty * PY + i < K + C::VY;
+        if (yin && ly + i >= K && ly + i < K + C::VY) rows_ok |= 1u << i;
 #pragma unroll
-        for (int k = 0; k < PXV; ++k) mxy[i][k] = yin && gx + k >= 0 && gx + k < g.n[0];
+        for (int k = 0; k < PXV; ++k)
+            if (yin && gx + k >= 0 && gx + k < g.n[0]) mask |= 1u << (i * PXV + k);
     }
-    const bool col_ok = tx * PXV >= C::HLX && tx * PXV < C::HLX + C::VX && gx < g.n[0];
+    const bool warp_all = __all_sync(0xffffffffu, mask == (1u << (PY * PXV)) - 1u);
+    const bool col_ok = lx >= C::HLX && lx < C::HLX + C::VX && gx < g.n[0];
     const bool col_full = gx + PXV <= g.n[0];
+    if (!col_ok) rows_ok = 0;
+    const int toff = ly * C::BX + lx;
+    const int up_off = ly > 0 ? -C::BX : 0;
+    const int dn_off = ly + PY < C::BY ? PY * C::BX : (PY - 1) * C::BX;
+    // plane bookkeeping in local indices p (global z = z_first + p)
+    const long long dlo = dom.lo - z_first, dhi = dom.hi - z_first;
+    const int p_dom_lo = dlo < -4 ? -4 : (int)dlo;
+    const int p_dom_hi = dhi > nin + 4 ? nin + 4 : (int)dhi;
+    const int p_out_lo = K, p_out_hi = nin - K;
 
     T3Level<T, PXV, PY> lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
 
-    T* __restrict__ dst = out + g.idx(gx, gy, 0);
     const long long plane_stride = g.pitch_x * g.pitch_y;
+    const long long row_stride = g.pitch_x;
+    // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
+    T* __restrict__ outp = out + g.idx(gx, gy, z_first - 2 * K + 1);
 
+    int st = 0;
+    uint32_t phase = 0;
+#pragma unroll 1
     for (int j = 0; j < nsteps; ++j) {
-        const int st = j % S;
-        if (j < nin) mbar_wait(&bars[st], (uint32_t)((j / S) & 1));
+        if (j < nin) mbar_wait(&bars[st], phase);
 #pragma unroll
         for (int l = 0; l < K; ++l) {
             // level l+1 is active on steps [l, nin + l)
             if (j >= l && j < nin + l) {
-                const T* src = l == 0 ? ring + (size_t)st * C::PLANE
-                                      : lbuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::PLANE;
-                const long long zo = z_first + (j - 2 * l) - 1;  // plane being emitted
-                const bool upd = zo >= dom.lo && zo < dom.hi;
+                const T* src = (l == 0 ? ring + (size_t)st * C::PLANE
+                                       : lbuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::PLANE) + toff;
+                const int pe = j - 2 * l - 1;  // local index of the plane being emitted
+                const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
                 T o[PY][PXV];
-                t3_level_step<T, K>(src, lv[l], tx, ty, avg, mxy, upd, o);
+                if (upd && warp_all) {
+                    t3_level_step<T, K, true>(src, up_off, dn_off, lv[l], avg, 0u, o);
+                } else {
+                    t3_level_step<T, K, false>(src, up_off, dn_off, lv[l], avg, upd ? mask : 0u, o);
+                }
                 if (l < K - 1) {
-                    T* wb = lbuf + (size_t)(2 * l + (j & 1)) * C::PLANE;
+                    T* wb = lbuf + (size_t)(2 * l + (j & 1)) * C::PLANE + toff;
 #pragma unroll
-                    for (int i = 0; i < PY; ++i)
-                        VecN<T, PXV>::st(wb + (ty * PY + i) * C::BX + tx * PXV, o[i]);
-                } else if (col_ok && zo >= zb && zo < ze) {
-                    T* p = dst + zo * plane_stride;
+                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::st(wb + i * C::BX, o[i]);
+                } else if (pe >= p_out_lo && pe < p_out_hi && rows_ok) {
 #pragma unroll
                     for (int i = 0; i < PY; ++i) {
-                        if (row_ok[i]) {
+                        if (rows_ok & (1u << i)) {
                             if (col_full) {
-                                VecN<T, PXV>::st(p + i * g.pitch_x, o[i]);
+                                VecN<T, PXV>::st(outp + i * row_stride, o[i]);
                             } else {
 #pragma unroll
                                 for (int k = 0; k < PXV; ++k)
-                                    if (gx + k < g.n[0]) p[i * g.pitch_x + k] = o[i][k];
+                                    if (gx + k < g.n[0]) outp[i * row_stride + k] = o[i][k];
                             }
                         }
                     }
                 }
             }
         }
+        outp += plane_stride;
         __syncthreads();
         if (tid == 0 && j + S < nin) {
             mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
-            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy,
-                        (int)(cz0 + j + S));
+            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + j + S);
+        }
+        if (++st == S) {
+            st = 0;
+            phase ^= 1u;
         }
     }
 }
