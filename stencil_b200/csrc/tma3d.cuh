@@ -32,10 +32,14 @@ template <class T, int K> struct T3 {
     static constexpr int HLX = (K + PXV - 1) / PXV * PXV;
     static constexpr int VX = (BX - HLX - K) / PXV * PXV;
     static constexpr int VY = BY - 2 * K;
-    static constexpr int STAGES = K <= 2 ? 4 : 3;
+    static constexpr int STAGES = 4;
     static constexpr int PLANE = BX * BY;  // elements
     static constexpr size_t PLANE_BYTES = (size_t)PLANE * sizeof(T);
-    static constexpr size_t SMEM = PLANE_BYTES * (STAGES + 2 * (K - 1)) + 8 * STAGES + 128;
+    // levels 1..K-1 only publish each thread's first and last row (what its y-neighbour
+    // threads need); the rows in between stay in the owner's registers
+    static constexpr int EDGE = TYN * 2 * BX;  // elements per edge buffer
+    static constexpr size_t SMEM =
+        PLANE_BYTES * STAGES + (size_t)EDGE * sizeof(T) * 2 * (K - 1) + 8 * STAGES + 128;
 };
 constexpr int T3_MAXK = 3;
 
@@ -104,21 +108,13 @@ template <class T, int PXV, int PY> struct T3Level {
     }
 };
 
-// Plane of level l-1 arrives (`s` = this thread's base pointer into the dense BY x BX
-// shared plane: row ly, column lx); emit the finished plane a-1 of level l into o[][].
-// FAST: every point this warp owns is updatable in x/y and the emitted plane is inside
-// the update domain, so no pass-through selects are needed (warp-uniform choice).
-template <class T, int K, bool FAST>
-__device__ __forceinline__ void t3_level_step(const T* __restrict__ s, int up_off, int dn_off,
-                                              T3Level<T, T3<T, K>::PXV, T3<T, K>::PY>& L, T avg,
-                                              unsigned mask, T (&o)[4][T3<T, K>::PXV]) {
-    using C = T3<T, K>;
-    constexpr int PXV = C::PXV, PY = C::PY;
-    T c[PY + 2][PXV];  // rows ly-1 .. ly+PY (clamped at the tile edge: halo shrink)
-    VecN<T, PXV>::ld(s + up_off, c[0]);
-#pragma unroll
-    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(s + i * C::BX, c[i + 1]);
-    VecN<T, PXV>::ld(s + dn_off, c[PY + 1]);
+// Rows ly-1 .. ly+PY of the arriving plane of level l-1 are in c[][]; emit the finished
+// plane a-1 of level l into o[][].  FAST: every point this warp owns is updatable in x/y
+// and the emitted plane is inside the update domain, so no pass-through selects are needed
+// (warp-uniform choice).
+template <class T, int PXV, int PY, bool FAST>
+__device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3Level<T, PXV, PY>& L, T avg,
+                                           unsigned mask, T (&o)[PY][PXV]) {
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
         const T lft = __shfl_up_sync(0xffffffffu, c[i + 1][PXV - 1], 1);
@@ -151,8 +147,8 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     // 128-byte align the TMA destinations
     unsigned char* base = smem_raw + ((128 - (smem_u32(smem_raw) & 127)) & 127);
     T* ring = reinterpret_cast<T*>(base);
-    T* lbuf = ring + (size_t)S * C::PLANE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(lbuf + (size_t)2 * (K - 1) * C::PLANE);
+    T* ebuf = ring + (size_t)S * C::PLANE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ebuf + (size_t)2 * (K - 1) * C::EDGE);
 
     const int tid = threadIdx.x;
     const int tx = tid & 31, ty = tid >> 5;
@@ -200,6 +196,10 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     const int toff = ly * C::BX + lx;
     const int up_off = ly > 0 ? -C::BX : 0;
     const int dn_off = ly + PY < C::BY ? PY * C::BX : (PY - 1) * C::BX;
+    // edge buffers: [thread row ty][0 = first row, 1 = last row][BX]
+    const int e_own = ty * 2 * C::BX + lx;
+    const int e_up = (ty > 0 ? (ty - 1) * 2 + 1 : 0) * C::BX + lx;
+    const int e_dn = (ty + 1 < C::TYN ? (ty + 1) * 2 : ty * 2 + 1) * C::BX + lx;
     // plane bookkeeping in local indices p (global z = z_first + p)
     const long long dlo = dom.lo - z_first, dhi = dom.hi - z_first;
     const int p_dom_lo = dlo < -4 ? -4 : (int)dlo;
@@ -209,6 +209,14 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     T3Level<T, PXV, PY> lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
+    // plane emitted by level l in the previous step (centre rows of level l+1's arrival)
+    T oprev[K > 1 ? K - 1 : 1][PY][PXV];
+#pragma unroll
+    for (int l = 0; l < K - 1; ++l)
+#pragma unroll
+        for (int i = 0; i < PY; ++i)
+#pragma unroll
+            for (int k = 0; k < PXV; ++k) oprev[l][i][k] = T(0);
 
     const long long plane_stride = g.pitch_x * g.pitch_y;
     const long long row_stride = g.pitch_x;
@@ -219,25 +227,45 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     uint32_t phase = 0;
 #pragma unroll 1
     for (int j = 0; j < nsteps; ++j) {
-        if (j < nin) mbar_wait(&bars[st], phase);
+        // higher levels first: they consume what the level below emitted in the previous
+        // step (registers + the edge rows published in shared memory)
 #pragma unroll
-        for (int l = 0; l < K; ++l) {
+        for (int l = K - 1; l >= 0; --l) {
             // level l+1 is active on steps [l, nin + l)
             if (j >= l && j < nin + l) {
-                const T* src = (l == 0 ? ring + (size_t)st * C::PLANE
-                                       : lbuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::PLANE) + toff;
+                T c[PY + 2][PXV];
+                if (l == 0) {
+                    mbar_wait(&bars[st], phase);
+                    const T* src = ring + (size_t)st * C::PLANE + toff;
+                    VecN<T, PXV>::ld(src + up_off, c[0]);
+#pragma unroll
+                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, c[i + 1]);
+                    VecN<T, PXV>::ld(src + dn_off, c[PY + 1]);
+                } else {
+                    const T* eb = ebuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::EDGE;
+                    VecN<T, PXV>::ld(eb + e_up, c[0]);
+                    VecN<T, PXV>::ld(eb + e_dn, c[PY + 1]);
+#pragma unroll
+                    for (int i = 0; i < PY; ++i)
+#pragma unroll
+                        for (int k = 0; k < PXV; ++k) c[i + 1][k] = oprev[l > 0 ? l - 1 : 0][i][k];
+                }
                 const int pe = j - 2 * l - 1;  // local index of the plane being emitted
                 const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
                 T o[PY][PXV];
                 if (upd && warp_all) {
-                    t3_level_step<T, K, true>(src, up_off, dn_off, lv[l], avg, 0u, o);
+                    t3_compute<T, PXV, PY, true>(c, lv[l], avg, 0u, o);
                 } else {
-                    t3_level_step<T, K, false>(src, up_off, dn_off, lv[l], avg, upd ? mask : 0u, o);
+                    t3_compute<T, PXV, PY, false>(c, lv[l], avg, upd ? mask : 0u, o);
                 }
                 if (l < K - 1) {
-                    T* wb = lbuf + (size_t)(2 * l + (j & 1)) * C::PLANE + toff;
+                    T* wb = ebuf + (size_t)(2 * l + (j & 1)) * C::EDGE + e_own;
+                    VecN<T, PXV>::st(wb, o[0]);
+                    VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
 #pragma unroll
-                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::st(wb + i * C::BX, o[i]);
+                    for (int i = 0; i < PY; ++i)
+#pragma unroll
+                        for (int k = 0; k < PXV; ++k) oprev[l < K - 1 ? l : 0][i][k] = o[i][k];
                 } else if (pe >= p_out_lo && pe < p_out_hi && rows_ok) {
 #pragma unroll
                     for (int i = 0; i < PY; ++i) {
