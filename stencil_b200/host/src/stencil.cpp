@@ -1,0 +1,256 @@
+// stencil.cpp — host side: problem set-up, dispatch to the B200 backend, self-check.
+//
+// Mirrors the structure of the reference's src/stencil/stencil.cpp: initialize_matrix()
+// (:14-21,190-207), run(method) timing only the accelerated sweep (:23-57), a name->method
+// map (:59-73) and check_result() with the naive loop (:75-151).
+#include <stencil/stencil.hpp>
+
+#include <stencil_b200.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <utility>
+
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+std::uint64_t mix64(std::uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+/// Problem definition. "ref" is Stencil::generate_initialized_matrix of the reference
+/// (stencil.cpp:190-207): zero interior, left/right halo = 1 (full padded height), other
+/// halo = 0.  "random" puts counter-based uniform [0,1) values in the interior.
+template <class T>
+void fill_initial(BoundaryMatrix<T>& m, bool random, std::uint64_t seed) {
+    m.fill_boundary(BoundaryPosition::Left, T(1));
+    m.fill_boundary(BoundaryPosition::Right, T(1));
+    if (!random) return;
+    auto const& s = m.shape();
+    for (std::size_t z = 0; z < m.depth(); ++z)
+        for (std::size_t y = 0; y < m.height(); ++y)
+            for (std::size_t x = 0; x < m.width(); ++x) {
+                std::uint64_t const lin =
+                    (std::uint64_t(z + s.halo[2]) * s.padded(1) + (y + s.halo[1])) * s.padded(0) + (x + s.halo[0]);
+                std::uint64_t const bits = mix64(seed + (lin + 1) * 0x9E3779B97F4A7C15ull);
+                m.elem_at(z, y, x) = static_cast<T>(static_cast<double>(bits >> 11) * 0x1.0p-53);
+            }
+}
+
+/// One naive sweep in the reference's summation order (stencil.cpp:103-125): per axis the
+/// low side far->near then the high side near->far; box: full cube, z outer, x inner.
+template <class T>
+void naive_step(BoundaryMatrixView<T> in, BoundaryMatrixView<T> out, int ndim, bool box, unsigned r, bool parallel) {
+    auto const& s = in.shape();
+    std::ptrdiff_t const stride[3] = {1, std::ptrdiff_t(s.row_stride), std::ptrdiff_t(s.plane_stride)};
+    unsigned count = 1;
+    for (int a = 0; a < ndim; ++a) count *= 2 * r + 1;
+    T const avg = box ? T(1) / T(count) : T(1) / T(2 * ndim * r);
+    std::ptrdiff_t const R = r, rz = ndim > 2 ? R : 0, ry = ndim > 1 ? R : 0;
+    std::ptrdiff_t const rows = std::ptrdiff_t(in.height() * in.depth());
+    (void)parallel;
+#pragma omp parallel for schedule(static) if (parallel)
+    for (std::ptrdiff_t row = 0; row < rows; ++row) {
+        std::size_t const z = std::size_t(row) / in.height(), y = std::size_t(row) % in.height();
+        T const* src = &in.elem_at(z, y, 0);
+        T* dst = &out.elem_at(z, y, 0);
+        for (std::size_t x = 0; x < in.width(); ++x) {
+            T const* c = src + x;
+            T sum = T(0);
+            if (!box) {
+                for (int a = 0; a < ndim; ++a) {
+                    for (std::ptrdiff_t k = R; k >= 1; --k) sum += c[-k * stride[a]];
+                    for (std::ptrdiff_t k = 1; k <= R; ++k) sum += c[k * stride[a]];
+                }
+            } else {
+                for (std::ptrdiff_t dz = -rz; dz <= rz; ++dz)
+                    for (std::ptrdiff_t dy = -ry; dy <= ry; ++dy)
+                        for (std::ptrdiff_t dx = -R; dx <= R; ++dx) sum += c[dz * stride[2] + dy * stride[1] + dx];
+            }
+            dst[x] = sum * avg;
+        }
+    }
+}
+
+template <class T>
+bool naive_sweep(BoundaryMatrix<T>& a, BoundaryMatrix<T>& b, ProgramOptions const& o, bool parallel) {
+    bool swapped = false;
+    for (unsigned i = 0; i != o.iterations; ++i) {
+        if (swapped) {
+            naive_step<T>(b.borrow(), a.borrow(), o.ndim(), o.stencil == "box", o.radius, parallel);
+        } else {
+            naive_step<T>(a.borrow(), b.borrow(), o.ndim(), o.stencil == "box", o.radius, parallel);
+        }
+        swapped = !swapped;
+    }
+    return swapped;
+}
+
+sb200_desc make_desc(ProgramOptions const& o) {
+    sb200_desc d;
+    std::memset(&d, 0, sizeof d);
+    d.ndim = o.ndim();
+    d.shape = o.stencil == "box" ? SB200_BOX : SB200_STAR;
+    d.dtype = o.dtype == "f64" ? SB200_F64 : SB200_F32;
+    d.radius = o.radius;
+    for (int a = 0; a < 3; ++a) d.n[a] = o.extent(a);
+    d.iterations = o.iterations;
+    d.time_block = o.time_block;
+    d.block_hint = o.block_size;
+    d.kernel = o.kernel == "generic" ? SB200_KERNEL_GENERIC
+               : o.kernel == "warp2d" ? SB200_KERNEL_WARP2D
+               : o.kernel == "tma3d"  ? SB200_KERNEL_TMA3D
+                                      : SB200_KERNEL_AUTO;
+    return d;
+}
+
+}  // namespace
+
+bool Stencil::parse_method(std::string_view name, InputMethod& out) {
+    static std::pair<std::string_view, InputMethod> const table[] = {
+        {"CUDA", CUDA}, {"CPU", CPU}, {"CPUOMP", CPU_OMP}, {"DMA", DMA},
+        {"DMAStaticUnroll", DMA_STATIC_UNROLL}, {"DMASlavePack", DMA_SLAVE_PACK}, {"RMA", RMA},
+    };
+    for (auto const& [n, m] : table)
+        if (n == name) {
+            out = m;
+            return true;
+        }
+    return false;
+}
+
+template <class T>
+void Stencil::initialize_typed() {
+    Pair<T> p;
+    std::array<std::size_t, 3> const ext {options.extent(0), options.extent(1), options.extent(2)};
+    p.matrix = BoundaryMatrix<T>::make(options.ndim(), ext, options.radius);
+    p.result = BoundaryMatrix<T>::make(options.ndim(), ext, options.radius);
+    fill_initial(p.matrix, options.init == "random", options.seed);
+    fill_initial(p.result, false, 0);
+    grids = std::move(p);
+}
+
+void Stencil::initialize_matrix() {
+    if (options.dtype == "f64") {
+        initialize_typed<double>();
+    } else {
+        initialize_typed<float>();
+    }
+}
+
+template <class T>
+auto Stencil::run_typed(InputMethod method) -> std::chrono::steady_clock::duration {
+    auto& p = std::get<Pair<T>>(grids);
+    info_ = RunInfo {};
+    auto const start = std::chrono::steady_clock::now();
+    switch (method) {
+    case CUDA: {
+        // The one call that replaces athread_spawn(...) + athread_join() (stencil.cpp:34-53).
+        sb200_desc const d = make_desc(options);
+        sb200_timing t;
+        if (sb200_run_host(&d, p.matrix.raw_data(), p.result.raw_data(), &t) != SB200_OK)
+            throw std::runtime_error(std::string("CUDA method failed: ") + sb200_last_error());
+        info_.h2d_ms = t.h2d_ms;
+        info_.sweep_ms = t.sweep_ms;
+        info_.d2h_ms = t.d2h_ms;
+        info_.launches = t.launches;
+        info_.time_block = t.time_block;
+        info_.kernel = t.kernel;
+        break;
+    }
+    case CPU:
+        naive_sweep(p.matrix, p.result, options, false);
+        break;
+    case CPU_OMP:
+        naive_sweep(p.matrix, p.result, options, true);
+#ifdef _OPENMP
+        info_.threads = omp_get_max_threads();
+#endif
+        break;
+    default:
+        throw std::runtime_error("Sunway athread methods (DMA, DMAStaticUnroll, DMASlavePack, RMA) are not "
+                                 "available on the B200 backend; use CUDA, CPU or CPUOMP");
+    }
+    return std::chrono::steady_clock::now() - start;
+}
+
+auto Stencil::run(InputMethod method) -> std::chrono::steady_clock::duration {
+    initialize_matrix();
+    return options.dtype == "f64" ? run_typed<double>(method) : run_typed<float>(method);
+}
+
+auto Stencil::run(std::string_view method_name) -> std::chrono::steady_clock::duration {
+    InputMethod m;
+    if (!parse_method(method_name, m)) throw std::runtime_error("unknown method name: " + std::string(method_name));
+    return run(m);
+}
+
+double Stencil::updates() const {
+    return double(options.extent(0)) * options.extent(1) * options.extent(2) * options.iterations;
+}
+
+template <class T>
+bool Stencil::check_typed() const {
+    auto const& p = std::get<Pair<T>>(grids);
+    std::array<std::size_t, 3> const ext {options.extent(0), options.extent(1), options.extent(2)};
+    auto a = BoundaryMatrix<T>::make(options.ndim(), ext, options.radius);
+    auto b = BoundaryMatrix<T>::make(options.ndim(), ext, options.radius);
+    fill_initial(a, options.init == "random", options.seed);
+    fill_initial(b, false, 0);
+    bool const swapped = naive_sweep(a, b, options, true);
+    BoundaryMatrix<T> const& want = swapped ? b : a;
+    BoundaryMatrix<T> const& got = swapped ? p.result : p.matrix;
+    bit_exact_ = true;
+    for (std::size_t z = 0; z != want.depth(); ++z)
+        for (std::size_t row = 0; row != want.height(); ++row)
+            for (std::size_t col = 0; col != want.width(); ++col) {
+                T const w = want.elem_at(z, row, col), g = got.elem_at(z, row, col);
+                if (std::memcmp(&w, &g, sizeof(T)) != 0) bit_exact_ = false;
+                if (!(std::fabs(double(w) - double(g)) < 1e-4)) {
+                    std::printf("invalid result at (%zu, %zu, %zu): %.15f vs %.15f\n", z, row, col, double(w), double(g));
+                    return false;
+                }
+            }
+    return true;
+}
+
+auto Stencil::check_result() const -> bool {
+    return options.dtype == "f64" ? check_typed<double>() : check_typed<float>();
+}
+
+auto Stencil::to_bmp() const -> BMPImage {
+    // Blue -> cyan -> green -> yellow -> red heat map of the FINAL field (the reference's
+    // to_bmp reads `matrix` regardless of parity, stencil.cpp:159; fixed here).
+    unsigned const w = options.extent(0), h = options.extent(1);
+    std::vector<BMPImage::Pixel> px;
+    px.reserve(std::size_t(w) * h);
+    bool const in_result = options.iterations & 1u;
+    auto value_at = [&](std::size_t row, std::size_t col) -> double {
+        return std::visit([&](auto const& p) { return double((in_result ? p.result : p.matrix).elem_at(0, row, col)); },
+                          grids);
+    };
+    auto ramp = [](double v) { return static_cast<unsigned char>(std::fmin(std::fmax(v, 0.0), 1.0) * 255.0); };
+    for (unsigned row = 0; row < h; ++row)
+        for (unsigned col = 0; col < w; ++col) {
+            double const v = std::fmin(std::fmax(value_at(row, col), 0.0), 1.0);
+            BMPImage::Pixel p;
+            if (v < 0.25) {
+                p.g = ramp(4 * v), p.b = 255;
+            } else if (v < 0.5) {
+                p.g = 255, p.b = ramp(1 + 4 * (0.25 - v));
+            } else if (v < 0.75) {
+                p.r = ramp(4 * (v - 0.5)), p.g = 255;
+            } else {
+                p.r = 255, p.g = ramp(1 + 4 * (0.75 - v));
+            }
+            px.push_back(p);
+        }
+    return BMPImage(std::move(px), w, h);
+}
