@@ -1,0 +1,45 @@
+"""Multi-GPU parity check (run under torchrun on N GPUs): the slab-decomposed sweep must be
+bitwise identical to the same grid swept on ONE GPU (checksum of checksums), for the 3-D
+TMA kernel and the 2-D warp kernel, including a remainder block."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from stencil_b200 import capi, slab, sweep
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+capi.check(capi.lib().sb200_init(local))
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+ok = True
+for n_local, shape, dtype, T, k in [((256, 200, 64), capi.STAR, capi.F64, 7, 2),
+                                     ((256, 200, 64), capi.STAR, capi.F32, 6, 3),
+                                     ((1000, 256), capi.BOX, capi.F32, 19, 4),
+                                     ((300, 128, 40), capi.BOX, capi.F64, 3, 1)]:
+    d = capi.make_desc(n_local, 1, shape, dtype, T, time_block=k)
+    sw = slab.SlabSweep(d, rank, world)
+    sw.fill(capi.INIT_RANDOM, seed=3)
+    sw.sweep(T)
+    cs = torch.tensor([sw.checksum() & 0x7FFFFFFFFFFFFFFF, sw.checksum() >> 63], dtype=torch.int64, device="cuda")
+    parts = [torch.zeros_like(cs) for _ in range(world)]
+    dist.all_gather(parts, cs)
+    total = sum(int(p[0].item()) + (int(p[1].item()) << 63) for p in parts) % (1 << 64)
+    if rank == 0:
+        n_full = list(n_local)
+        n_full[-1] *= world
+        df = capi.make_desc(n_full, 1, shape, dtype, T, time_block=k)
+        g = sweep.DeviceGrids(df)
+        g.fill(capi.INIT_RANDOM, seed=3)
+        g.sweep(T)
+        want = g.checksum()
+        good = want == total
+        ok &= good
+        print(f"n_local={n_local} shape={shape} dtype={dtype} T={T} k={k} world={world}: "
+              f"{'bitwise identical' if good else 'MISMATCH'} ({want:#x} vs {total:#x})", flush=True)
+        del g
+    dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)
