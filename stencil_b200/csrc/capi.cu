@@ -164,33 +164,40 @@ int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap*
     return SB200_OK;
 }
 
-template <class T, int K>
+template <class T, int K, int SHAPE>
 int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, long long ob,
                    long long oe, cudaStream_t st) {
     using C = T3<T, K>;
     if (oe <= ob) return SB200_OK;
     static bool attr = false;
     if (!attr) {
-        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         attr = true;
     }
     const CUtensorMap* map = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, &map)) return rc;
     const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, S.sm_count);
-    const T avg = Avg<T>::value(STAR, 3, 1);
-    sweep_tma3d_kernel<T, K><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
+    const T avg = Avg<T>::value(SHAPE, 3, 1);
+    sweep_tma3d_kernel<T, K, SHAPE><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
         *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg);
     CU_TRY(cudaGetLastError());
     return SB200_OK;
 }
 
 template <class T>
-int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, Domain dom, int K, long long ob,
-                 long long oe, cudaStream_t st) {
+int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domain dom, int K,
+                 long long ob, long long oe, cudaStream_t st) {
+    if (shape == SB200_BOX) {
+        switch (K) {
+            case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st);
+            case 2: return launch_tma3d_k<T, 2, BOX>(in, out, dtype, g, dom, ob, oe, st);
+            default: return fail(SB200_ERR_INVALID, "TMA3D box time block %d out of range", K);
+        }
+    }
     switch (K) {
-        case 1: return launch_tma3d_k<T, 1>(in, out, dtype, g, dom, ob, oe, st);
-        case 2: return launch_tma3d_k<T, 2>(in, out, dtype, g, dom, ob, oe, st);
-        case 3: return launch_tma3d_k<T, 3>(in, out, dtype, g, dom, ob, oe, st);
+        case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st);
+        case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st);
+        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st);
         default: return fail(SB200_ERR_INVALID, "TMA3D time block %d out of range", K);
     }
 }
@@ -205,12 +212,13 @@ struct Choice {
 Choice choose(const sb200_desc* d) {
     Choice c;
     const bool w2d_ok = d->ndim == 2 && d->radius == 1;
-    const bool t3_ok = d->ndim == 3 && d->radius == 1 && d->shape == SB200_STAR;
+    const bool t3_ok = d->ndim == 3 && d->radius == 1;
     int kern = d->kernel;
     if (kern == SB200_KERNEL_AUTO)
         kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : SB200_KERNEL_GENERIC;
     c.kernel = kern;
-    c.max_k = kern == SB200_KERNEL_WARP2D ? W2D_MAXK : kern == SB200_KERNEL_TMA3D ? T3_MAXK : 1;
+    c.max_k = kern == SB200_KERNEL_WARP2D ? W2D_MAXK
+              : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK) : 1;
     int k = (int)d->time_block;
     if (k == 0) k = kern == SB200_KERNEL_WARP2D ? 4 : kern == SB200_KERNEL_TMA3D ? 2 : 1;
     if (k > c.max_k) k = c.max_k;
@@ -221,8 +229,8 @@ Choice choose(const sb200_desc* d) {
 int check_choice(const sb200_desc* d, const Choice& c) {
     if (c.kernel == SB200_KERNEL_WARP2D && !(d->ndim == 2 && d->radius == 1))
         return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2, radius=1");
-    if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1 && d->shape == SB200_STAR))
-        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1, star");
+    if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
+        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1");
     return SB200_OK;
 }
 
@@ -239,7 +247,7 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, S.sm_count, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
-            return launch_tma3d<T>(a, b, d->dtype, g, dom, k, ob, oe, st);
+            return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
     }
     return fail(SB200_ERR_INVALID, "bad kernel");
 }

@@ -41,7 +41,8 @@ template <class T, int K> struct T3 {
     static constexpr size_t SMEM =
         PLANE_BYTES * STAGES + (size_t)EDGE * sizeof(T) * 2 * (K - 1) + 8 * STAGES + 128;
 };
-constexpr int T3_MAXK = 3;
+constexpr int T3_MAXK = 3;      // star
+constexpr int T3_MAXK_BOX = 2;  // box (27-point)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -136,7 +137,63 @@ __device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3Level<T,
     }
 }
 
-template <class T, int K>
+// ---- 27-point box ---------------------------------------------------------------------
+// Oracle order: sum over dz (outer), dy, dx (inner), ascending, starting
+// from 0, then one multiply.  An arriving plane is the dz=-1 plane of output a+1, the dz=0
+// plane of output a and the dz=+1 plane of output a-1, so three accumulator chains advance
+// by nine sequential adds each; no partial sums are shared (that would reorder the adds).
+template <class T, int PXV, int PY> struct T3LevelBox {
+    T a[PY][PXV];    // chain of the output whose first plane (dz=-1) has been added
+    T b[PY][PXV];    // chain of the output whose first two planes have been added
+    T cm1[PY][PXV];  // centre of plane a-1 (pass-through value)
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int i = 0; i < PY; ++i)
+#pragma unroll
+            for (int k = 0; k < PXV; ++k) a[i][k] = b[i][k] = cm1[i][k] = T(0);
+    }
+};
+
+template <class T, int PXV, int PY, bool FAST>
+__device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3LevelBox<T, PXV, PY>& L, T avg,
+                                           unsigned mask, T (&o)[PY][PXV]) {
+    T lft[PY + 2], rgt[PY + 2];
+#pragma unroll
+    for (int i = 0; i < PY + 2; ++i) {
+        lft[i] = __shfl_up_sync(0xffffffffu, c[i][PXV - 1], 1);
+        rgt[i] = __shfl_down_sync(0xffffffffu, c[i][0], 1);
+    }
+#pragma unroll
+    for (int i = 0; i < PY; ++i) {
+#pragma unroll
+        for (int k = 0; k < PXV; ++k) {
+            T f = L.b[i][k], nb = L.a[i][k], na = T(0);
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy) {
+                const T xl = k == 0 ? lft[i + dy] : c[i + dy][k - 1];
+                const T xc = c[i + dy][k];
+                const T xr = k == PXV - 1 ? rgt[i + dy] : c[i + dy][k + 1];
+                f = add_rn(add_rn(add_rn(f, xl), xc), xr);
+                nb = add_rn(add_rn(add_rn(nb, xl), xc), xr);
+                na = add_rn(add_rn(add_rn(na, xl), xc), xr);
+            }
+            f = mul_rn(f, avg);
+            if (FAST) {
+                o[i][k] = f;
+            } else {
+                o[i][k] = ((mask >> (i * PXV + k)) & 1u) ? f : L.cm1[i][k];
+            }
+            L.b[i][k] = nb;
+            L.a[i][k] = na;
+            L.cm1[i][k] = c[i + 1][k];
+        }
+    }
+}
+
+template <class T, int PXV, int PY, int SHAPE> struct T3LevelSel { using type = T3Level<T, PXV, PY>; };
+template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOX> { using type = T3LevelBox<T, PXV, PY>; };
+
+template <class T, int K, int SHAPE>
 __global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
 sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out, Grid g,
                    Domain dom, long long ob, long long oe, int ntx, int nty, int chunk_planes,
@@ -206,7 +263,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     const int p_dom_hi = dhi > nin + 4 ? nin + 4 : (int)dhi;
     const int p_out_lo = K, p_out_hi = nin - K;
 
-    T3Level<T, PXV, PY> lv[K];
+    typename T3LevelSel<T, PXV, PY, SHAPE>::type lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
     // plane emitted by level l in the previous step (centre rows of level l+1's arrival)

@@ -27,12 +27,14 @@ def resolve_kernel(desc: capi.Desc):
     """(family, fused depth) the library will use for this descriptor (mirrors choose()
     in csrc/capi.cu; max depth is asked from the library)."""
     w2d = desc.ndim == 2 and desc.radius == 1
-    t3 = desc.ndim == 3 and desc.radius == 1 and desc.shape == capi.STAR
+    t3 = desc.ndim == 3 and desc.radius == 1
+    box = desc.shape == capi.BOX
     kern = desc.kernel
     if kern == capi.KERNEL_AUTO:
         kern = capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3 else capi.KERNEL_GENERIC
-    max_k = {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 8, capi.KERNEL_TMA3D: 3}[kern]
-    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 4, capi.KERNEL_TMA3D: 2}[kern]
+    max_k = {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 8, capi.KERNEL_TMA3D: 2 if box else 3}[kern]
+    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 4,
+                            capi.KERNEL_TMA3D: 2}[kern]
     return kern, min(k, max_k)
 
 

@@ -81,10 +81,21 @@ def test_tma3d_kernel(gpu, n, T, k, dtype):
     assert t.kernel == capi.KERNEL_TMA3D and t.launches == -(-T // k)
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,T,k", [
+    ((1, 1, 1), 3, 2), ((5, 4, 3), 3, 1), ((60, 62, 20), 4, 2), ((61, 59, 33), 3, 1),
+    ((130, 70, 40), 5, 2), ((250, 130, 17), 2, 1), ((123, 125, 64), 3, 2),
+])
+def test_tma3d_box27_kernel(gpu, n, T, k, dtype):
+    t = _check(n, 1, capi.BOX, dtype, T, time_block=k, kernel=capi.KERNEL_TMA3D)
+    assert t.kernel == capi.KERNEL_TMA3D and t.launches == -(-T // k)
+
+
 def test_auto_dispatch(gpu):
     assert _check((200, 100), 1, capi.BOX, np.float32, 8).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70, 60), 1, capi.STAR, np.float64, 4).kernel == capi.KERNEL_TMA3D
-    assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
+    assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
 
 

@@ -61,3 +61,6 @@ if "c4" in which:
     run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 6, capi.KERNEL_GENERIC, 1)
 if "c3" in which:
     run("c3-27pt", (512, 512, 512), capi.BOX, capi.F64, 6, capi.KERNEL_GENERIC, 1)
+    for k in (1, 2):
+        run("c3-27pt", (512, 512, 512), capi.BOX, capi.F64, 12, capi.KERNEL_TMA3D, k)
+        run("c3-27pt-f32", (512, 512, 512), capi.BOX, capi.F32, 12, capi.KERNEL_TMA3D, k)
