@@ -23,7 +23,7 @@ namespace sb200 {
 constexpr int W2D_PX = 4;                 // x points per lane
 constexpr int W2D_WIDTH = 32 * W2D_PX;    // strip width incl. halo
 constexpr int W2D_WARPS = 4;              // warps (independent strips) per block
-constexpr int W2D_DEPTH = 4;              // rows prefetched per lane
+constexpr int W2D_DEPTH = 8;              // ring slots per warp (DEPTH-1 rows in flight)
 constexpr int W2D_MAXK = 8;
 
 __host__ __device__ constexpr int w2d_halo_left(int K) { return (K + 3) & ~3; }
@@ -31,19 +31,31 @@ __host__ __device__ constexpr int w2d_valid(int K) { return (W2D_WIDTH - w2d_hal
 
 template <class T> struct Row4 { T v[4]; };
 
+// cp.async (LDGSTS) staging: each lane copies the 4 x it owns (16 B for f32, 2 x 16 B for
+// f64) from global straight into a warp-private shared-memory ring, bypassing registers and
+// L1; the lane later reads back exactly the bytes it copied, so cp.async.wait_group alone
+// orders the accesses (no barrier).
 template <class T>
-__device__ __forceinline__ Row4<T> w2d_load(const T* __restrict__ p, bool ok) {
+__device__ __forceinline__ void w2d_async_row(T* sdst, const T* __restrict__ gsrc) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(sdst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gsrc) : "memory");
+    if constexpr (sizeof(T) == 8)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa + 16), "l"(gsrc + 2) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void w2d_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+template <class T>
+__device__ __forceinline__ Row4<T> w2d_read_row(const T* sp) {
     Row4<T> r;
-    if (!ok) {
-        r.v[0] = r.v[1] = r.v[2] = r.v[3] = T(0);
-        return r;
-    }
     if constexpr (sizeof(T) == 4) {
-        const float4 f = __ldg(reinterpret_cast<const float4*>(p));
+        const float4 f = *reinterpret_cast<const float4*>(sp);
         r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w;
     } else {
-        const double2 a = __ldg(reinterpret_cast<const double2*>(p));
-        const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+        const double2 a = reinterpret_cast<const double2*>(sp)[0];
+        const double2 b = reinterpret_cast<const double2*>(sp)[1];
         r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y;
     }
     return r;
@@ -71,7 +83,8 @@ template <class T> struct W2dLevel<T, STAR> {
     }
     // Row `c` (with left/right neighbour values l, rg) arrives; emits the finished
     // previous row into `o`.  `upd[i]`: point i of the emitted row is updatable.
-    __device__ __forceinline__ void step(const Row4<T>& c, T l, T rg, T avg, const bool* upd,
+    template <bool EDGE>
+    __device__ __forceinline__ void step(const Row4<T>& c, T l, T rg, T avg, unsigned upd,
                                          Row4<T>& o) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -79,7 +92,7 @@ template <class T> struct W2dLevel<T, STAR> {
             const T xr = i == 3 ? rg : c.v[i + 1];
             const T h = add_rn(add_rn(T(0), xl), xr);
             const T f = mul_rn(add_rn(t[i], c.v[i]), avg);
-            o.v[i] = upd[i] ? f : cm1[i];
+            o.v[i] = (!EDGE || ((upd >> i) & 1u)) ? f : cm1[i];
             t[i] = add_rn(h, cm1[i]);
             cm1[i] = c.v[i];
         }
@@ -94,17 +107,18 @@ template <class T> struct W2dLevel<T, BOX> {
 #pragma unroll
         for (int i = 0; i < 4; ++i) a[i] = b[i] = cm1[i] = T(0);
     }
-    __device__ __forceinline__ void step(const Row4<T>& c, T l, T rg, T avg, const bool* upd,
+    template <bool EDGE>
+    __device__ __forceinline__ void step(const Row4<T>& c, T l, T rg, T avg, unsigned upd,
                                          Row4<T>& o) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const T xl = i == 0 ? l : c.v[i - 1];
             const T xr = i == 3 ? rg : c.v[i + 1];
             const T f = mul_rn(add_rn(add_rn(add_rn(b[i], xl), c.v[i]), xr), avg);
-            o.v[i] = upd[i] ? f : cm1[i];
+            o.v[i] = (!EDGE || ((upd >> i) & 1u)) ? f : cm1[i];
             b[i] = add_rn(add_rn(add_rn(a[i], xl), c.v[i]), xr);
             a[i] = add_rn(add_rn(add_rn(T(0), xl), c.v[i]), xr);
-            cm1[i] = c.v[i];
+            if (EDGE) cm1[i] = c.v[i];  // only the pass-through needs it
         }
     }
 };
@@ -113,6 +127,75 @@ template <class T>
 __device__ __forceinline__ T shfl_up1(T v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 template <class T>
 __device__ __forceinline__ T shfl_down1(T v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+
+// Stream one (strip, chunk) item through the K fused levels.  EDGE = false is the
+// select-free variant for items that lie entirely inside the update domain (every streamed
+// row and every column of the strip, halo columns included, is an updatable point), which
+// is the case for all but the outermost strips / chunks.
+template <class T, int SHAPE, int K, bool EDGE>
+__device__ __forceinline__ void w2d_stream(const T* __restrict__ src, T* __restrict__ dst,
+                                           long long pitch, int nsteps, int j_dom_lo, int j_dom_hi,
+                                           int j_row_lo, int j_row_hi, unsigned mxmask, T* ring,
+                                           bool lane_valid, int ncols_valid, T avg) {
+    W2dLevel<T, SHAPE> lv[K];
+#pragma unroll
+    for (int l = 0; l < K; ++l) lv[l].init();
+    // Row index j counts streamed rows: global row = y_first + j; src/dst point at row
+    // y_first.  Loads are UNCONDITIONAL (no predicated zero-fill that would serialise the
+    // register prefetch queue): rows past the end of the item or outside the allocation are
+    // clamped to a valid row — whatever they return lies outside the dependence cone of
+    // every valid output (beyond the Dirichlet halo, which passes through).
+    const int j_ld_lo = EDGE ? (j_row_lo > 0 ? j_row_lo : 0) : 0;
+    const int j_ld_hi = (EDGE && j_row_hi < nsteps ? j_row_hi : nsteps) - 1;
+    auto row_ptr = [&](int jn) -> const T* {
+        int jc = jn < j_ld_hi ? jn : j_ld_hi;
+        if (EDGE) jc = jc > j_ld_lo ? jc : j_ld_lo;
+        return src + (long long)jc * pitch;
+    };
+    // prologue: rows 0 .. DEPTH-2 in flight
+#pragma unroll
+    for (int d = 0; d < W2D_DEPTH - 1; ++d) w2d_async_row(ring + d * W2D_WIDTH, row_ptr(d));
+    T* __restrict__ sp = dst - (long long)K * pitch;  // row emitted by the last level at j
+    for (int j0 = 0; j0 < nsteps; j0 += W2D_DEPTH) {
+#pragma unroll
+        for (int d = 0; d < W2D_DEPTH; ++d) {
+            // steps past nsteps (loop rounded up to the ring depth) compute on clamped
+            // rows and store nothing
+            const int j = j0 + d;
+            {
+                // refill the slot that was consumed in the previous step, then wait until
+                // all but the newest DEPTH-1 copies (i.e. row j) have landed
+                w2d_async_row(ring + ((d + W2D_DEPTH - 1) % W2D_DEPTH) * W2D_WIDTH, row_ptr(j + W2D_DEPTH - 1));
+                w2d_async_wait<W2D_DEPTH - 1>();
+                Row4<T> cur = w2d_read_row(ring + d * W2D_WIDTH);
+#pragma unroll
+                for (int l = 0; l < K; ++l) {
+                    // level l+1: row j - l arrives, row j - l - 1 is emitted
+                    unsigned upd = 0;
+                    if (EDGE) {
+                        const int jo = j - l - 1;
+                        upd = (jo >= j_dom_lo && jo < j_dom_hi) ? mxmask : 0u;
+                    }
+                    const T lft = shfl_up1(cur.v[3]);
+                    const T rgt = shfl_down1(cur.v[0]);
+                    Row4<T> o;
+                    lv[l].template step<EDGE>(cur, lft, rgt, avg, upd, o);
+                    cur = o;
+                }
+                if (lane_valid && j >= 2 * K && j < nsteps) {  // emitted row j - K is an output row
+                    if (ncols_valid >= W2D_PX) {
+                        w2d_store(sp, cur);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (i < ncols_valid) sp[i] = cur.v[i];
+                    }
+                }
+            }
+            sp += pitch;
+        }
+    }
+}
 
 // in -> out, K fused steps, output rows [ob, oe) (slab-interior coordinates).
 template <class T, int SHAPE, int K>
@@ -131,68 +214,39 @@ sweep_warp2d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domai
     const long long ye = (yb + chunk_rows < oe) ? yb + chunk_rows : oe;
 
     const long long gx = (long long)strip * V - HL + lane * W2D_PX;  // first x of this lane
-    // loads stay inside the allocation (columns beyond it are zero)
-    const bool col_ok = gx >= -(long long)g.ox && gx + W2D_PX <= g.pitch_x - g.ox;
-    bool mx[4];
+    // loads stay inside the allocation: lanes beyond it re-read the nearest valid column
+    // group (their values never reach a valid output)
+    long long gx_ld = gx < -(long long)g.ox ? -(long long)g.ox : gx;
+    if (gx_ld + W2D_PX > g.pitch_x - g.ox) gx_ld = g.pitch_x - g.ox - W2D_PX;
+    unsigned mxmask = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) mx[i] = gx + i >= 0 && gx + i < g.n[0];
+    for (int i = 0; i < 4; ++i)
+        if (gx + i >= 0 && gx + i < g.n[0]) mxmask |= 1u << i;
     const bool lane_valid = lane * W2D_PX >= HL && lane * W2D_PX < HL + V && gx < g.n[0];
-    const long long row_lo = -(long long)g.oy, row_hi = g.pitch_y - g.oy;  // allocated rows
+    const long long rem = g.n[0] - gx;
+    const int ncols_valid = rem >= W2D_PX ? W2D_PX : (rem > 0 ? (int)rem : 0);
 
-    W2dLevel<T, SHAPE> lv[K];
-#pragma unroll
-    for (int l = 0; l < K; ++l) lv[l].init();
+    const long long y_first = yb - K;           // first row to arrive at level 1
+    const int nsteps = (int)(ye - yb) + 2 * K;  // rows streamed through
+    // bounds as streamed-row indices j (global row = y_first + j), clamped to int range
+    auto rel = [&](long long y) -> int {
+        const long long v = y - y_first;
+        return v < -8 ? -8 : (v > nsteps + 8 ? nsteps + 8 : (int)v);
+    };
+    const int j_dom_lo = rel(dom.lo), j_dom_hi = rel(dom.hi);
+    const int j_row_lo = rel(-(long long)g.oy), j_row_hi = rel(g.pitch_y - g.oy);  // allocated rows
+    const T* __restrict__ src = in + g.idx(gx_ld, y_first, 0);
+    T* __restrict__ dst = out + g.idx(gx, y_first, 0);
 
-    const long long y_first = yb - K;                  // first row to arrive at level 1
-    const int nsteps = (int)(ye - yb) + 2 * K;         // rows streamed through
-    const T* __restrict__ src = in + g.idx(gx, 0, 0);
-    T* __restrict__ dst = out + g.idx(gx, 0, 0);
-
-    Row4<T> q[W2D_DEPTH];
-#pragma unroll
-    for (int d = 0; d < W2D_DEPTH; ++d) {
-        const long long y = y_first + d;
-        q[d] = w2d_load(src + y * g.pitch_x, col_ok && d < nsteps && y >= row_lo && y < row_hi);
-    }
-
-    for (int j0 = 0; j0 < nsteps; j0 += W2D_DEPTH) {
-#pragma unroll
-        for (int d = 0; d < W2D_DEPTH; ++d) {
-            const int j = j0 + d;
-            if (j < nsteps) {
-                Row4<T> cur = q[d];
-                {
-                    const long long y = y_first + j + W2D_DEPTH;
-                    q[d] = w2d_load(src + y * g.pitch_x, col_ok && j + W2D_DEPTH < nsteps &&
-                                                             y >= row_lo && y < row_hi);
-                }
-#pragma unroll
-                for (int l = 0; l < K; ++l) {
-                    // level l+1: row (y_first + j - l) arrives, row (y_first + j - l - 1) is emitted
-                    const long long yo = y_first + j - l - 1;
-                    const bool row_upd = yo >= dom.lo && yo < dom.hi;
-                    bool upd[4];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) upd[i] = mx[i] && row_upd;
-                    const T lft = shfl_up1(cur.v[3]);
-                    const T rgt = shfl_down1(cur.v[0]);
-                    Row4<T> o;
-                    lv[l].step(cur, lft, rgt, avg, upd, o);
-                    cur = o;
-                }
-                const long long yo = y_first + j - K;  // row emitted by the last level
-                if (lane_valid && yo >= yb && yo < ye) {
-                    T* p = dst + yo * g.pitch_x;
-                    if (gx + W2D_PX <= g.n[0]) {
-                        w2d_store(p, cur);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (gx + i < g.n[0]) p[i] = cur.v[i];
-                    }
-                }
-            }
-        }
+    __shared__ __align__(16) T ring_all[W2D_WARPS][W2D_DEPTH][W2D_WIDTH];
+    T* ring = &ring_all[threadIdx.x >> 5][0][lane * W2D_PX];
+    const bool interior = __all_sync(0xffffffffu, mxmask == 0xFu) && j_dom_lo <= 0 && j_dom_hi >= nsteps;
+    if (interior) {
+        w2d_stream<T, SHAPE, K, false>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
+                                       mxmask, ring, lane_valid, ncols_valid, avg);
+    } else {
+        w2d_stream<T, SHAPE, K, true>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
+                                      mxmask, ring, lane_valid, ncols_valid, avg);
     }
 }
 
