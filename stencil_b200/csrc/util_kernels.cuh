@@ -43,6 +43,25 @@ __global__ void fill_kernel(T* __restrict__ grid, Grid g, int random, uint64_t s
     }
 }
 
+// Dense host-layout image (row pitch = hx, as uploaded with one contiguous copy) -> the
+// pitched device layout; padding columns are zeroed so no uninitialised bits are ever read.
+template <class T>
+__global__ void unpack_dense_kernel(const T* __restrict__ dense, T* __restrict__ a, Grid g,
+                                    long long hx) {
+    const long long rows = g.pitch_y * g.planes;
+    const long long x0 = g.ox - g.r;  // pitched column of dense column 0
+    for (long long row = blockIdx.y; row < rows; row += gridDim.y) {
+        const T* src = dense + row * hx;
+        T* da = a + row * g.pitch_x;
+        for (long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x; px < g.pitch_x;
+             px += (long long)gridDim.x * blockDim.x) {
+            const long long dx = px - x0;
+            const T v = (dx >= 0 && dx < hx) ? src[dx] : T(0);
+            da[px] = v;
+        }
+    }
+}
+
 template <class T> struct Bits;
 template <> struct Bits<float> {
     static __device__ uint64_t of(float v) { return (uint64_t)__float_as_uint(v); }
