@@ -34,6 +34,16 @@ METRIC = "GStencil/s (grid-point updates/s), 3D 7-point fp64 heat stencil 512^3,
 UNIT = "GStencil/s"
 
 
+def ncu_traffic(key):
+    """DRAM bytes per launch of the dominant kernel, from the committed ncu capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f)[key]
+        return float(e["bytes"]), e["source"]
+    except Exception:  # noqa: BLE001
+        return None, None
+
+
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -214,6 +224,7 @@ def main():
     alg_bytes = 16.0 * pts_rank * k
     peak, peak_kind = measured_peak_gbs()
     achieved = alg_bytes / (avg_launch_ms * 1e-3) / 1e9
+    traffic, traffic_src = (ncu_traffic(f"tma3d_f64_star_k{k}_512") if world == 1 else (None, None))
 
     # e2e through the host-buffer C-ABI call (pinned host memory), rank-local grid
     e2e = None
@@ -263,7 +274,8 @@ def main():
                        "l2": "inputs (2 x 1.15 GB per GPU) larger than the 126 MB L2",
                        "init": "counter-based uniform [0,1) seed 1"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_kind": peak_kind,
                          "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_ms},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }))
