@@ -97,42 +97,41 @@ template <> struct VecN<double, 2> {
     }
 };
 
-// Per-thread state of one time level: PY rows x PXV points.
-template <class T, int PXV, int PY> struct T3Level {
-    T t[PY][PXV];    // (in-plane partial of plane a-1) + centre of plane a-2
-    T cm1[PY][PXV];  // centre of plane a-1 (also its pass-through value)
+// Per-thread partial-sum state of one time level (PY rows x PXV points).  The centre rows of
+// the two most recent planes of every level live in two-slot register rings owned by the
+// kernel (indexed by the plane-loop phase, a compile-time constant after unrolling by two),
+// so advancing a plane never copies registers.
+template <class T, int PXV, int PY> struct T3Star {
+    T t[PY][PXV];  // (in-plane partial of plane a-1) + centre of plane a-2
     __device__ __forceinline__ void init() {
 #pragma unroll
         for (int i = 0; i < PY; ++i)
 #pragma unroll
-            for (int k = 0; k < PXV; ++k) t[i][k] = cm1[i][k] = T(0);
+            for (int k = 0; k < PXV; ++k) t[i][k] = T(0);
     }
 };
 
-// Rows ly-1 .. ly+PY of the arriving plane of level l-1 are in c[][]; emit the finished
-// plane a-1 of level l into o[][].  FAST: every point this warp owns is updatable in x/y
-// and the emitted plane is inside the update domain, so no pass-through selects are needed
-// (warp-uniform choice).
-template <class T, int PXV, int PY, bool FAST>
-__device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3Level<T, PXV, PY>& L, T avg,
-                                           unsigned mask, T (&o)[PY][PXV]) {
+// Plane a of the level below arrives: centre rows c[0..PY), the row above (up) and below
+// (dn) this thread's rows; cm1 = centre rows of plane a-1.  Emits plane a-1 of this level
+// into o[][] for every point as if it were updatable (the caller restores pass-through
+// points), and advances the partial sums to plane a.
+template <class T, int PXV, int PY>
+__device__ __forceinline__ void t3_level(const T (&up)[PXV], const T (&c)[PY][PXV], const T (&dn)[PXV],
+                                         const T (&cm1)[PY][PXV], T3Star<T, PXV, PY>& L, T avg,
+                                         T (&o)[PY][PXV]) {
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
-        const T lft = __shfl_up_sync(0xffffffffu, c[i + 1][PXV - 1], 1);
-        const T rgt = __shfl_down_sync(0xffffffffu, c[i + 1][0], 1);
+        const T lft = __shfl_up_sync(0xffffffffu, c[i][PXV - 1], 1);
+        const T rgt = __shfl_down_sync(0xffffffffu, c[i][0], 1);
 #pragma unroll
         for (int k = 0; k < PXV; ++k) {
-            const T xl = k == 0 ? lft : c[i + 1][k - 1];
-            const T xr = k == PXV - 1 ? rgt : c[i + 1][k + 1];
-            const T sum = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), c[i][k]), c[i + 2][k]);
-            const T f = mul_rn(add_rn(L.t[i][k], c[i + 1][k]), avg);
-            if (FAST) {
-                o[i][k] = f;
-            } else {
-                o[i][k] = ((mask >> (i * PXV + k)) & 1u) ? f : L.cm1[i][k];
-            }
-            L.t[i][k] = add_rn(sum, L.cm1[i][k]);
-            L.cm1[i][k] = c[i + 1][k];
+            const T xl = k == 0 ? lft : c[i][k - 1];
+            const T xr = k == PXV - 1 ? rgt : c[i][k + 1];
+            const T yl = i == 0 ? up[k] : c[i - 1][k];
+            const T yr = i == PY - 1 ? dn[k] : c[i + 1][k];
+            const T sum = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), yl), yr);
+            o[i][k] = mul_rn(add_rn(L.t[i][k], c[i][k]), avg);
+            L.t[i][k] = add_rn(sum, cm1[i][k]);
         }
     }
 }
@@ -142,27 +141,31 @@ __device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3Level<T,
 // from 0, then one multiply.  An arriving plane is the dz=-1 plane of output a+1, the dz=0
 // plane of output a and the dz=+1 plane of output a-1, so three accumulator chains advance
 // by nine sequential adds each; no partial sums are shared (that would reorder the adds).
-template <class T, int PXV, int PY> struct T3LevelBox {
-    T a[PY][PXV];    // chain of the output whose first plane (dz=-1) has been added
-    T b[PY][PXV];    // chain of the output whose first two planes have been added
-    T cm1[PY][PXV];  // centre of plane a-1 (pass-through value)
+template <class T, int PXV, int PY> struct T3Box {
+    T a[PY][PXV];  // chain of the output whose first plane (dz=-1) has been added
+    T b[PY][PXV];  // chain of the output whose first two planes have been added
     __device__ __forceinline__ void init() {
 #pragma unroll
         for (int i = 0; i < PY; ++i)
 #pragma unroll
-            for (int k = 0; k < PXV; ++k) a[i][k] = b[i][k] = cm1[i][k] = T(0);
+            for (int k = 0; k < PXV; ++k) a[i][k] = b[i][k] = T(0);
     }
 };
 
-template <class T, int PXV, int PY, bool FAST>
-__device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3LevelBox<T, PXV, PY>& L, T avg,
-                                           unsigned mask, T (&o)[PY][PXV]) {
+template <class T, int PXV, int PY>
+__device__ __forceinline__ void t3_level(const T (&up)[PXV], const T (&c)[PY][PXV], const T (&dn)[PXV],
+                                         const T (&)[PY][PXV], T3Box<T, PXV, PY>& L, T avg,
+                                         T (&o)[PY][PXV]) {
     T lft[PY + 2], rgt[PY + 2];
+    lft[0] = __shfl_up_sync(0xffffffffu, up[PXV - 1], 1);
+    rgt[0] = __shfl_down_sync(0xffffffffu, up[0], 1);
 #pragma unroll
-    for (int i = 0; i < PY + 2; ++i) {
-        lft[i] = __shfl_up_sync(0xffffffffu, c[i][PXV - 1], 1);
-        rgt[i] = __shfl_down_sync(0xffffffffu, c[i][0], 1);
+    for (int i = 0; i < PY; ++i) {
+        lft[i + 1] = __shfl_up_sync(0xffffffffu, c[i][PXV - 1], 1);
+        rgt[i + 1] = __shfl_down_sync(0xffffffffu, c[i][0], 1);
     }
+    lft[PY + 1] = __shfl_up_sync(0xffffffffu, dn[PXV - 1], 1);
+    rgt[PY + 1] = __shfl_down_sync(0xffffffffu, dn[0], 1);
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
 #pragma unroll
@@ -170,28 +173,26 @@ __device__ __forceinline__ void t3_compute(const T (&c)[PY + 2][PXV], T3LevelBox
             T f = L.b[i][k], nb = L.a[i][k], na = T(0);
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy) {
-                const T xl = k == 0 ? lft[i + dy] : c[i + dy][k - 1];
-                const T xc = c[i + dy][k];
-                const T xr = k == PXV - 1 ? rgt[i + dy] : c[i + dy][k + 1];
+                const int r = i + dy;  // 0 = up, 1..PY = c, PY+1 = dn
+                const T* row = r == 0 ? up : (r == PY + 1 ? dn : c[r - 1]);
+                const T xl = k == 0 ? lft[r] : row[k - 1];
+                const T xc = row[k];
+                const T xr = k == PXV - 1 ? rgt[r] : row[k + 1];
                 f = add_rn(add_rn(add_rn(f, xl), xc), xr);
                 nb = add_rn(add_rn(add_rn(nb, xl), xc), xr);
                 na = add_rn(add_rn(add_rn(na, xl), xc), xr);
             }
-            f = mul_rn(f, avg);
-            if (FAST) {
-                o[i][k] = f;
-            } else {
-                o[i][k] = ((mask >> (i * PXV + k)) & 1u) ? f : L.cm1[i][k];
-            }
+            o[i][k] = mul_rn(f, avg);
             L.b[i][k] = nb;
             L.a[i][k] = na;
-            L.cm1[i][k] = c[i + 1][k];
         }
     }
 }
 
-template <class T, int PXV, int PY, int SHAPE> struct T3LevelSel { using type = T3Level<T, PXV, PY>; };
-template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOX> { using type = T3LevelBox<T, PXV, PY>; };
+template <class T, int PXV, int PY, int SHAPE> struct T3LevelSel { using type = T3Star<T, PXV, PY>; };
+template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOX> { using type = T3Box<T, PXV, PY>; };
+
+template <int V> struct IC { static constexpr int value = V; };
 
 template <class T, int K, int SHAPE>
 __global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
@@ -200,6 +201,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
                    T avg) {
     using C = T3<T, K>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
+    static_assert((S & (S - 1)) == 0 && S >= 2, "stage count must be a power of two");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     // 128-byte align the TMA destinations
     unsigned char* base = smem_raw + ((128 - (smem_u32(smem_raw) & 127)) & 127);
@@ -250,6 +252,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     const bool col_ok = lx >= C::HLX && lx < C::HLX + C::VX && gx < g.n[0];
     const bool col_full = gx + PXV <= g.n[0];
     if (!col_ok) rows_ok = 0;
+    const bool store_fast = col_full && rows_ok == (1u << PY) - 1u;
     const int toff = ly * C::BX + lx;
     const int up_off = ly > 0 ? -C::BX : 0;
     const int dn_off = ly + PY < C::BY ? PY * C::BX : (PY - 1) * C::BX;
@@ -263,67 +266,86 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     const int p_dom_hi = dhi > nin + 4 ? nin + 4 : (int)dhi;
     const int p_out_lo = K, p_out_hi = nin - K;
 
+    // Register state.  R: level-0 centre rows of the two newest planes; O[l]: the two newest
+    // planes emitted by level l+1 (l < K-1); slot = plane-loop phase.  Every level runs on
+    // every step: before its first real plane a level only sees the zero-initialised rings
+    // (its state stays zero), and what the levels compute after the last streamed plane lies
+    // beyond the last stored plane.
+    T R[2][PY][PXV];
+    T O[K > 1 ? K - 1 : 1][2][PY][PXV];
     typename T3LevelSel<T, PXV, PY, SHAPE>::type lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
-    // plane emitted by level l in the previous step (centre rows of level l+1's arrival)
-    T oprev[K > 1 ? K - 1 : 1][PY][PXV];
 #pragma unroll
-    for (int l = 0; l < K - 1; ++l)
+    for (int s = 0; s < 2; ++s)
 #pragma unroll
         for (int i = 0; i < PY; ++i)
 #pragma unroll
-            for (int k = 0; k < PXV; ++k) oprev[l][i][k] = T(0);
+            for (int k = 0; k < PXV; ++k) {
+                R[s][i][k] = T(0);
+#pragma unroll
+                for (int l = 0; l < K - 1; ++l) O[l][s][i][k] = T(0);
+            }
 
     const long long plane_stride = g.pitch_x * g.pitch_y;
     const long long row_stride = g.pitch_x;
     // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
     T* __restrict__ outp = out + g.idx(gx, gy, z_first - 2 * K + 1);
 
-    int st = 0;
-    uint32_t phase = 0;
-#pragma unroll 1
-    for (int j = 0; j < nsteps; ++j) {
-        // higher levels first: they consume what the level below emitted in the previous
-        // step (registers + the edge rows published in shared memory)
+    // One time level of one plane step.  L = level index (level L+1 of the fused block),
+    // P = j & 1.  Level L consumes the plane its lower level emitted on the PREVIOUS step
+    // (registers + the edge rows published in shared memory), so one barrier per step
+    // orders everything.
+    auto level = [&](auto Lc, auto Pc, int j) {
+        constexpr int L = decltype(Lc)::value, P = decltype(Pc)::value;
+        T up[PXV], dn[PXV];
+        if constexpr (L == 0) {
+            const int st = j & (S - 1);
+            if (j < nin) mbar_wait(&bars[st], (uint32_t)(j / S) & 1u);
+            const T* src = ring + (size_t)st * C::PLANE + toff;
+            VecN<T, PXV>::ld(src + up_off, up);
 #pragma unroll
-        for (int l = K - 1; l >= 0; --l) {
-            // level l+1 is active on steps [l, nin + l)
-            if (j >= l && j < nin + l) {
-                T c[PY + 2][PXV];
-                if (l == 0) {
-                    mbar_wait(&bars[st], phase);
-                    const T* src = ring + (size_t)st * C::PLANE + toff;
-                    VecN<T, PXV>::ld(src + up_off, c[0]);
+            for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[P][i]);
+            VecN<T, PXV>::ld(src + dn_off, dn);
+        } else {
+            const T* eb = ebuf + (size_t)(2 * (L - 1) + (P ^ 1)) * C::EDGE;
+            VecN<T, PXV>::ld(eb + e_up, up);
+            VecN<T, PXV>::ld(eb + e_dn, dn);
+        }
+        const T (&c)[PY][PXV] = *(L == 0 ? &R[P] : &O[L > 0 ? L - 1 : 0][P ^ 1]);
+        const T (&cm1)[PY][PXV] = *(L == 0 ? &R[P ^ 1] : &O[L > 0 ? L - 1 : 0][P]);
+        const int pe = j - 2 * L - 1;  // local index of the plane being emitted
+        const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
+        if constexpr (L < K - 1) {
+            T (&o)[PY][PXV] = O[L][P];
+            t3_level<T, PXV, PY>(up, c, dn, cm1, lv[L], avg, o);
+            if (!(upd && warp_all)) {
+                const unsigned m = upd ? mask : 0u;
 #pragma unroll
-                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, c[i + 1]);
-                    VecN<T, PXV>::ld(src + dn_off, c[PY + 1]);
-                } else {
-                    const T* eb = ebuf + (size_t)(2 * (l - 1) + ((j - 1) & 1)) * C::EDGE;
-                    VecN<T, PXV>::ld(eb + e_up, c[0]);
-                    VecN<T, PXV>::ld(eb + e_dn, c[PY + 1]);
+                for (int i = 0; i < PY; ++i)
 #pragma unroll
-                    for (int i = 0; i < PY; ++i)
+                    for (int k = 0; k < PXV; ++k)
+                        if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
+            }
+            T* wb = ebuf + (size_t)(2 * L + P) * C::EDGE + e_own;
+            VecN<T, PXV>::st(wb, o[0]);
+            VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
+        } else {
+            T o[PY][PXV];
+            t3_level<T, PXV, PY>(up, c, dn, cm1, lv[L], avg, o);
+            if (!(upd && warp_all)) {
+                const unsigned m = upd ? mask : 0u;
 #pragma unroll
-                        for (int k = 0; k < PXV; ++k) c[i + 1][k] = oprev[l > 0 ? l - 1 : 0][i][k];
-                }
-                const int pe = j - 2 * l - 1;  // local index of the plane being emitted
-                const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
-                T o[PY][PXV];
-                if (upd && warp_all) {
-                    t3_compute<T, PXV, PY, true>(c, lv[l], avg, 0u, o);
-                } else {
-                    t3_compute<T, PXV, PY, false>(c, lv[l], avg, upd ? mask : 0u, o);
-                }
-                if (l < K - 1) {
-                    T* wb = ebuf + (size_t)(2 * l + (j & 1)) * C::EDGE + e_own;
-                    VecN<T, PXV>::st(wb, o[0]);
-                    VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
+                for (int i = 0; i < PY; ++i)
 #pragma unroll
-                    for (int i = 0; i < PY; ++i)
+                    for (int k = 0; k < PXV; ++k)
+                        if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
+            }
+            if (pe >= p_out_lo && pe < p_out_hi) {
+                if (store_fast) {
 #pragma unroll
-                        for (int k = 0; k < PXV; ++k) oprev[l < K - 1 ? l : 0][i][k] = o[i][k];
-                } else if (pe >= p_out_lo && pe < p_out_hi && rows_ok) {
+                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::st(outp + i * row_stride, o[i]);
+                } else if (rows_ok) {
 #pragma unroll
                     for (int i = 0; i < PY; ++i) {
                         if (rows_ok & (1u << i)) {
@@ -339,16 +361,25 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
                 }
             }
         }
+    };
+    auto step = [&](auto Pc, int j) {
+        // higher levels first: they consume what the level below emitted one step earlier
+        if constexpr (K > 2) level(IC<2>{}, Pc, j);
+        if constexpr (K > 1) level(IC<1>{}, Pc, j);
+        level(IC<0>{}, Pc, j);
         outp += plane_stride;
         __syncthreads();
         if (tid == 0 && j + S < nin) {
+            const int st = j & (S - 1);
             mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
             tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + j + S);
         }
-        if (++st == S) {
-            st = 0;
-            phase ^= 1u;
-        }
+    };
+    // steps past nsteps (loop rounded up to the phase count) wait for nothing and store nothing
+#pragma unroll 1
+    for (int j = 0; j < nsteps; j += 2) {
+        step(IC<0>{}, j);
+        step(IC<1>{}, j + 1);
     }
 }
 
