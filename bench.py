@@ -165,6 +165,8 @@ def main():
     ap.add_argument("--time-block", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="multi-GPU halo exchange: fused peer stores (p2p) or NCCL send/recv")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -188,7 +190,7 @@ def main():
     n = (N_SIDE, N_SIDE, N_SIDE)
     pts_rank = N_SIDE ** 3
     desc = capi.make_desc(n, 1, capi.STAR, capi.F64, T_STEPS, time_block=args.time_block)
-    runner = slab.SlabSweep(desc, rank, world)
+    runner = slab.SlabSweep(desc, rank, world, exchange=args.exchange)
     runner.fill(capi.INIT_RANDOM, seed=1)
 
     def barrier():
@@ -270,7 +272,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "3D 7-point star r=1, 512^3 fp64 per GPU, T=100 (BASELINE configs[1])",
                        "grid": [N_SIDE, N_SIDE, N_SIDE * world], "time_block": k,
-                       "kernel": runner.kernel_name, "parallelism": f"z-slab x{world}",
+                       "kernel": runner.kernel_name, "parallelism": f"z-slab x{world}", "halo_exchange": runner.exchange,
                        "l2": "inputs (2 x 1.15 GB per GPU) larger than the 126 MB L2",
                        "init": "counter-based uniform [0,1) seed 1"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -279,6 +281,7 @@ def main():
                          "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_launch_ms},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }))
+    runner.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -151,6 +151,53 @@ int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* gr
 int sb200_host_alloc(void** ptr, size_t bytes);
 int sb200_host_free(void* ptr);
 
+/* ---- multi-GPU slab link: halo exchange fused into the sweep kernel ------------
+ * One process per GPU.  Replaces the reference's on-chip RMA halo puts + reply
+ * counters (src/stencil/slave/stencil_rma.cpp:198-255) at GPU scale: the face
+ * CTAs of a launch store their planes into the local grid AND straight into the
+ * ghost planes of the neighbours' destination buffers over NVLink (peer-mapped
+ * pointers obtained with the sb200_ipc_* calls), then count themselves in on an
+ * arrival counter in the neighbour's memory; the neighbour's next launch acquires
+ * that counter before it reads its ghost planes.  No NCCL call, no extra launch
+ * and no host synchronisation on the data path.
+ *
+ * All ranks must own slabs of identical shape, issue the same sequence of linked
+ * launches, and must not touch a buffer from the host side (fill, free) while a
+ * neighbour may still be sweeping (barrier first). */
+#define SB200_IPC_HANDLE_BYTES 64
+#define SB200_LINK_FLAG_WORDS 4 /* [0] arrivals from the lower neighbour, [1] from the
+                                   upper one, [2] set to 1 if a wait timed out, [3] spare */
+typedef struct sb200_slab_link {
+    void* peer_dst_lo;      /* lower neighbour's DESTINATION buffer of this launch, NULL at the global boundary */
+    void* peer_dst_hi;      /* upper neighbour's */
+    uint32_t* flags_local;  /* SB200_LINK_FLAG_WORDS words in local device memory, zeroed once at setup */
+    uint32_t* flags_lo;     /* lower neighbour's flag words (peer-mapped) */
+    uint32_t* flags_hi;     /* upper neighbour's */
+    uint32_t wait_arrivals; /* sum of *arrivals returned by all previous linked launches */
+} sb200_slab_link;
+
+/* Zero-filled device memory from cudaMalloc (exportable, unlike sub-allocations). */
+int sb200_device_alloc(void** ptr, size_t bytes);
+int sb200_device_free(void* ptr);
+/* CUDA IPC: export a sb200_device_alloc pointer / map a neighbour's export. */
+int sb200_ipc_export(void* dev_ptr, unsigned char handle[SB200_IPC_HANDLE_BYTES]);
+int sb200_ipc_open(const unsigned char handle[SB200_IPC_HANDLE_BYTES], void** dev_ptr);
+int sb200_ipc_close(void* dev_ptr);
+
+/* One fused block of `steps` (<= max time block) steps a -> b over the whole slab
+ * in ONE launch: the CTAs of the first and last z chunk are dispatched first and
+ * push the face planes to the neighbours (peer stores + arrival signal).
+ * Needs ghost == radius * max-steps-between-exchanges >= radius * steps and a
+ * slab of at least 2*ghost planes; 3-D radius-1 (TMA3D family) only.
+ * *arrivals = face CTAs per face of this launch (add it to wait_arrivals). */
+int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
+                            int hi_is_boundary, const void* a, void* b, uint32_t steps,
+                            const sb200_slab_link* link, void* stream, uint32_t* arrivals);
+
+/* Blocking read of the SB200_LINK_FLAG_WORDS flag words (after synchronising the
+ * device): words[2] != 0 means a face CTA timed out waiting for a neighbour. */
+int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLAG_WORDS]);
+
 /* Largest time block the chosen kernel family supports for this descriptor. */
 int sb200_max_time_block(const sb200_desc* desc);
 

@@ -24,7 +24,11 @@ SYMBOLS = [
     "sb200_finalize", "sb200_run_host", "sb200_layout_for", "sb200_sweep_device",
     "sb200_sweep_device_range", "sb200_fill_device", "sb200_upload", "sb200_download",
     "sb200_checksum_device", "sb200_host_alloc", "sb200_host_free", "sb200_max_time_block",
+    "sb200_device_alloc", "sb200_device_free", "sb200_ipc_export", "sb200_ipc_open",
+    "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
 ]
+IPC_HANDLE_BYTES = 64
+LINK_FLAG_WORDS = 4
 
 
 class Desc(ctypes.Structure):
@@ -50,6 +54,14 @@ class Layout(ctypes.Structure):
         ("pitch_x", ctypes.c_uint64), ("pitch_y", ctypes.c_uint64), ("planes", ctypes.c_uint64),
         ("ox", ctypes.c_uint64), ("oy", ctypes.c_uint64), ("oz", ctypes.c_uint64),
         ("bytes", ctypes.c_uint64),
+    ]
+
+
+class SlabLink(ctypes.Structure):
+    _fields_ = [
+        ("peer_dst_lo", ctypes.c_void_p), ("peer_dst_hi", ctypes.c_void_p),
+        ("flags_local", ctypes.c_void_p), ("flags_lo", ctypes.c_void_p),
+        ("flags_hi", ctypes.c_void_p), ("wait_arrivals", ctypes.c_uint32),
     ]
 
 
@@ -91,6 +103,14 @@ def lib() -> ctypes.CDLL:
         L.sb200_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_host_free.argtypes = [vp]
         L.sb200_max_time_block.argtypes = [dp]
+        L.sb200_device_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
+        L.sb200_device_free.argtypes = [vp]
+        L.sb200_ipc_export.argtypes = [vp, ctypes.c_char_p]
+        L.sb200_ipc_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(vp)]
+        L.sb200_ipc_close.argtypes = [vp]
+        L.sb200_link_status.argtypes = [vp, ctypes.POINTER(u32)]
+        L.sb200_sweep_slab_linked.argtypes = [dp, u32, i32, i32, vp, vp, u32,
+                                              ctypes.POINTER(SlabLink), vp, ctypes.POINTER(u32)]
         _lib = L
     return _lib
 

@@ -166,38 +166,51 @@ int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap*
 
 template <class T, int K, int SHAPE>
 int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, long long ob,
-                   long long oe, cudaStream_t st) {
+                   long long oe, cudaStream_t st, const SlabLinkDev& link_in) {
     using C = T3<T, K>;
     if (oe <= ob) return SB200_OK;
     static bool attr = false;
     if (!attr) {
-        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         attr = true;
     }
     const CUtensorMap* map = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, &map)) return rc;
     const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, S.sm_count);
     const T avg = Avg<T>::value(SHAPE, 3, 1);
-    sweep_tma3d_kernel<T, K, SHAPE><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
-        *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg);
+    if (link_in.link_lo || link_in.link_hi) {
+        SlabLinkDev link = link_in;
+        long long nc = p.nchunks;
+        if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
+        if (nc < 1) nc = 1;
+        link.nchunks = (int)nc;
+        sweep_tma3d_kernel<T, K, SHAPE, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
+            *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
+    } else {
+        sweep_tma3d_kernel<T, K, SHAPE, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
+            *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link_in);
+    }
     CU_TRY(cudaGetLastError());
     return SB200_OK;
 }
 
+const SlabLinkDev kNoLink = {};
+
 template <class T>
 int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domain dom, int K,
-                 long long ob, long long oe, cudaStream_t st) {
+                 long long ob, long long oe, cudaStream_t st, const SlabLinkDev& link = kNoLink) {
     if (shape == SB200_BOX) {
         switch (K) {
-            case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st);
-            case 2: return launch_tma3d_k<T, 2, BOX>(in, out, dtype, g, dom, ob, oe, st);
+            case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st, link);
+            case 2: return launch_tma3d_k<T, 2, BOX>(in, out, dtype, g, dom, ob, oe, st, link);
             default: return fail(SB200_ERR_INVALID, "TMA3D box time block %d out of range", K);
         }
     }
     switch (K) {
-        case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st);
-        case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st);
-        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st);
+        case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
+        case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
+        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
         default: return fail(SB200_ERR_INVALID, "TMA3D time block %d out of range", K);
     }
 }
@@ -398,6 +411,119 @@ int sb200_sweep_device_range(const sb200_desc* desc, uint32_t ghost, int lo_is_b
     const Domain dom = make_domain(g, lo_is_boundary, hi_is_boundary);
     if (launches) *launches = z_end > z_begin ? 1 : 0;
     return pass(desc, c, g, dom, a, b, (int)steps, (long long)z_begin, (long long)z_end, (cudaStream_t)stream);
+}
+
+int sb200_device_alloc(void** ptr, size_t bytes) {
+    if (!ptr || bytes == 0) return fail(SB200_ERR_INVALID, "bad allocation request");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    CU_TRY(cudaMalloc(ptr, bytes));
+    CU_TRY(cudaMemset(*ptr, 0, bytes));
+    CU_TRY(cudaDeviceSynchronize());
+    return SB200_OK;
+}
+
+int sb200_device_free(void* ptr) {
+    if (!ptr) return SB200_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (size_t i = 0; i < S.maps.size();)  // tensor maps of a freed buffer must not be reused
+        if (S.maps[i].key.ptr == ptr) S.maps.erase(S.maps.begin() + i); else ++i;
+    CU_TRY(cudaFree(ptr));
+    return SB200_OK;
+}
+
+int sb200_ipc_export(void* dev_ptr, unsigned char handle[SB200_IPC_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == SB200_IPC_HANDLE_BYTES, "IPC handle size");
+    if (!dev_ptr || !handle) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    cudaIpcMemHandle_t h;
+    CU_TRY(cudaIpcGetMemHandle(&h, dev_ptr));
+    memcpy(handle, &h, sizeof h);
+    return SB200_OK;
+}
+
+int sb200_ipc_open(const unsigned char handle[SB200_IPC_HANDLE_BYTES], void** dev_ptr) {
+    if (!dev_ptr || !handle) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    CU_TRY(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return SB200_OK;
+}
+
+int sb200_ipc_close(void* dev_ptr) {
+    if (!dev_ptr) return SB200_OK;
+    CU_TRY(cudaIpcCloseMemHandle(dev_ptr));
+    return SB200_OK;
+}
+
+int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLAG_WORDS]) {
+    if (!flags_local || !words) return fail(SB200_ERR_INVALID, "null argument");
+    CU_TRY(cudaDeviceSynchronize());
+    CU_TRY(cudaMemcpy(words, flags_local, sizeof(uint32_t) * SB200_LINK_FLAG_WORDS, cudaMemcpyDeviceToHost));
+    return SB200_OK;
+}
+
+int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
+                            int hi_is_boundary, const void* a, void* b, uint32_t steps,
+                            const sb200_slab_link* link, void* stream, uint32_t* arrivals) {
+    if (int rc = validate(desc)) return rc;
+    if (!a || !b || !link) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    const Choice c = choose(desc);
+    if (int rc = check_choice(desc, c)) return rc;
+    if (c.kernel != SB200_KERNEL_TMA3D)
+        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D family (3-D, radius 1)");
+    if (steps < 1 || (int)steps > c.max_k)
+        return fail(SB200_ERR_INVALID, "linked sweep fuses 1..%d steps (got %u)", c.max_k, steps);
+    const Grid g = make_grid(desc, ghost);
+    const long long n = outer_n(g);
+    if (ghost < steps * desc->radius)
+        return fail(SB200_ERR_INVALID, "%u steps need %u ghost planes, have %u", steps, steps * desc->radius, ghost);
+    if (n < 2LL * ghost) return fail(SB200_ERR_INVALID, "slab of %lld planes is thinner than two ghost zones", n);
+    if (!link->flags_local) return fail(SB200_ERR_INVALID, "null flag block");
+    if ((!lo_is_boundary && (!link->peer_dst_lo || !link->flags_lo)) ||
+        (!hi_is_boundary && (!link->peer_dst_hi || !link->flags_hi)))
+        return fail(SB200_ERR_INVALID, "missing neighbour mapping for an internal face");
+    SlabLinkDev L = {};
+    L.link_lo = lo_is_boundary ? 0 : 1;
+    L.link_hi = hi_is_boundary ? 0 : 1;
+    L.face_planes = (int)ghost;
+    const long long plane = g.pitch_x * g.pitch_y;
+    L.peer_out_lo = link->peer_dst_lo;
+    L.shift_lo = n * plane;  // my plane z is the lower neighbour's plane z + n (its upper ghosts)
+    L.peer_out_hi = link->peer_dst_hi;
+    L.shift_hi = -n * plane;
+    L.wait_lo = link->flags_local + 0;
+    L.wait_hi = link->flags_local + 1;
+    L.signal_lo = link->flags_lo ? link->flags_lo + 1 : nullptr;  // I am its upper neighbour
+    L.signal_hi = link->flags_hi ? link->flags_hi + 0 : nullptr;
+    L.wait_value = link->wait_arrivals;
+    L.err_flag = link->flags_local + 2;
+    const Domain dom = make_domain(g, lo_is_boundary, hi_is_boundary);
+    const long long ob = 0, oe = n;
+    int ntx, nty;
+    if (desc->dtype == SB200_F64) {
+        switch (steps) {
+            case 1: { auto p = t3_plan<double, 1>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 2: { auto p = t3_plan<double, 2>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<double, 3>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+        }
+    } else {
+        switch (steps) {
+            case 1: { auto p = t3_plan<float, 1>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 2: { auto p = t3_plan<float, 2>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<float, 3>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+        }
+    }
+    if (arrivals) *arrivals = (uint32_t)(ntx * nty);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (desc->dtype == SB200_F64)
+        return launch_tma3d<double>((const double*)a, (double*)b, desc->dtype, g, desc->shape, dom, (int)steps, ob, oe, st, L);
+    return launch_tma3d<float>((const float*)a, (float*)b, desc->dtype, g, desc->shape, dom, (int)steps, ob, oe, st, L);
 }
 
 int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int init, uint64_t seed,

@@ -19,6 +19,12 @@
 #pragma once
 #include <cuda.h>
 
+#include <algorithm>
+#include <array>
+#include <functional>
+#include <map>
+#include <vector>
+
 #include "common.cuh"
 
 namespace sb200 {
@@ -194,11 +200,66 @@ template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOX> { using t
 
 template <int V> struct IC { static constexpr int value = V; };
 
-template <class T, int K, int SHAPE>
+// ---- slab link: face planes stored straight into the neighbours' ghost planes ----------
+// Multi-GPU slabs (one process per GPU).  No extra CTAs and no extra launch: the CTAs of the
+// slab's first z chunk also own its low face (planes [0, g)), those of the last chunk its
+// high face ([n-g, n)).  A face plane is stored twice: into the local grid and, over NVLink,
+// into the ghost planes of the neighbour's destination buffer (peer-mapped pointer).
+// The push happens at the END of the CTA (the plane loop itself carries no link code), which
+// is why the last and the first chunk are dispatched FIRST; arrival is signalled with one
+// release-add per CTA on a counter in the neighbour's memory, and the neighbour's
+// face-owning CTAs of the NEXT launch acquire the counter before they touch their ghosts.  The
+// same counter orders the write-after-read hazard: a CTA signals only after its last read of
+// the ghost planes the neighbour's next launch overwrites.  This is the B200 counterpart of
+// the reference's RMA halo puts + reply counters (stencil_rma.cpp:198-255).
+struct SlabLinkDev {
+    int link_lo, link_hi;     // low / high end of the slab is an internal face
+    int face_planes;          // g
+    int nchunks;              // z chunks of this launch
+    void* peer_out_lo;        // lower / upper neighbour's destination buffer (same layout)
+    void* peer_out_hi;
+    long long shift_lo;       // element offset of the same plane in that buffer
+    long long shift_hi;
+    unsigned* wait_lo;        // local arrival counters fed by the lower / upper neighbour
+    unsigned* wait_hi;
+    unsigned* signal_lo;      // the neighbours' counters this rank feeds
+    unsigned* signal_hi;
+    unsigned wait_value;      // arrivals required before this launch may read its ghosts
+    unsigned* err_flag;       // set to 1 if a wait timed out (never hangs the GPU)
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_sys_add_u32(unsigned* p, unsigned v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Bounded acquire-spin on an arrival counter: gives up after 2 s, and at once if another
+// CTA already gave up — a broken link ends in a reported error (sb200_link_status), never
+// in a hung GPU.
+__device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsigned* err_flag) {
+    const unsigned long long t0 = global_timer_ns();
+    while ((int)(ld_acquire_sys_u32(flag) - want) < 0) {
+        if (global_timer_ns() - t0 > 2000000000ull || *(volatile unsigned*)err_flag != 0u) {
+            *(volatile unsigned*)err_flag = 1u;
+            break;
+        }
+        __nanosleep(100);
+    }
+}
+
+template <class T, int K, int SHAPE, bool LINKED>
 __global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
 sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out, Grid g,
                    Domain dom, long long ob, long long oe, int ntx, int nty, int chunk_planes,
-                   T avg) {
+                   T avg, const SlabLinkDev link) {
     using C = T3<T, K>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
     static_assert((S & (S - 1)) == 0 && S >= 2, "stage count must be a power of two");
@@ -211,11 +272,21 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
 
     const int tid = threadIdx.x;
     const int tx = tid & 31, ty = tid >> 5;
-    const int b = blockIdx.x;
-    const int tix = b % ntx, tiy = (b / ntx) % nty;
-    const long long chunk = b / (ntx * nty);
-    const long long zb = ob + chunk * chunk_planes;
-    const long long ze = zb + chunk_planes < oe ? zb + chunk_planes : oe;
+    const int tiles = ntx * nty;
+    const int tile = (int)(blockIdx.x % (unsigned)tiles);
+    const int tix = tile % ntx, tiy = tile / ntx;
+    const int slot = (int)(blockIdx.x / (unsigned)tiles);
+    // linked launches dispatch the LAST chunk first: its CTAs deliver the high face only at
+    // the end of their z stream
+    int chunk = slot;
+    if (LINKED && link.link_hi) chunk = slot == 0 ? link.nchunks - 1 : slot - 1;
+    const bool is_lo = LINKED && link.link_lo && chunk == 0;                // owns the low face
+    const bool is_hi = LINKED && link.link_hi && chunk == link.nchunks - 1;  // owns the high face
+    // linked launches balance the chunks (every chunk >= g planes, so the first / last chunk
+    // contains the whole low / high face)
+    const long long zb = LINKED ? ob + (oe - ob) * chunk / link.nchunks : ob + (long long)chunk * chunk_planes;
+    const long long ze = LINKED ? ob + (oe - ob) * (chunk + 1) / link.nchunks
+                                : (zb + chunk_planes < oe ? zb + chunk_planes : oe);
     const long long gx0 = (long long)tix * C::VX - C::HLX;  // interior coords of tile (0,0)
     const long long gy0 = (long long)tiy * C::VY - K;
     const long long z_first = zb - K;
@@ -225,6 +296,14 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     if (tid == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (LINKED && (is_lo || is_hi) && link.wait_value != 0) {
+            // the neighbours' previous launch must have delivered its face planes into the
+            // ghost planes this chunk is about to stream
+            if (is_lo) link_wait(link.wait_lo, link.wait_value, link.err_flag);
+            if (is_hi) link_wait(link.wait_hi, link.wait_value, link.err_flag);
+            // TMA reads go through the async proxy
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
     }
     __syncthreads();
     const int cx = (int)(gx0 + g.ox), cy = (int)(gy0 + g.oy);
@@ -291,7 +370,6 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
     const long long row_stride = g.pitch_x;
     // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
     T* __restrict__ outp = out + g.idx(gx, gy, z_first - 2 * K + 1);
-
     // One time level of one plane step.  L = level index (level L+1 of the fused block),
     // P = j & 1.  Level L consumes the plane its lower level emitted on the PREVIOUS step
     // (registers + the edge rows published in shared memory), so one barrier per step
@@ -381,6 +459,45 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
         step(IC<0>{}, j);
         step(IC<1>{}, j + 1);
     }
+    if (LINKED && (is_lo || is_hi)) {
+        // Face push, after the z stream so the plane loop carries no link code at all: every
+        // thread copies the face-plane points IT stored (its own writes, so no barrier is
+        // needed before the read-back) into the neighbour's ghost planes with 128-bit
+        // stores over NVLink; after the barrier thread 0 publishes them system-wide and
+        // counts this CTA in on the neighbour's arrival counter.
+        T* home = out + g.idx(gx, gy, 0);
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) {
+            if (side == 0 ? !is_lo : !is_hi) continue;
+            const long long z0 = side == 0 ? 0 : g.n[2] - link.face_planes;
+            const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
+                                     (side == 0 ? link.shift_lo : link.shift_hi);
+#pragma unroll 1
+            for (int p = 0; p < link.face_planes; ++p) {
+                T* src = home + (z0 + p) * plane_stride;
+#pragma unroll
+                for (int i = 0; i < PY; ++i) {
+                    if (rows_ok & (1u << i)) {
+                        if (col_full) {
+                            T v[PXV];
+                            VecN<T, PXV>::ld(src + i * row_stride, v);
+                            VecN<T, PXV>::st(src + rdelta + i * row_stride, v);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < PXV; ++k)
+                                if (gx + k < g.n[0]) src[rdelta + i * row_stride + k] = src[i * row_stride + k];
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
+            if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
+        }
+    }
 }
 
 struct T3Plan {
@@ -388,6 +505,9 @@ struct T3Plan {
     long long nchunks, blocks;
 };
 
+// Chunk count along z.  Every CTA streams its chunk plus 3K-1 pipeline planes, CTAs are
+// dispatched in blockIdx order to the first free SM (1 CTA per SM): pick the chunk count
+// with the smallest simulated makespan (in plane-steps).
 template <class T, int K>
 static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count) {
     using C = T3<T, K>;
@@ -395,23 +515,44 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
     p.ntx = (int)((nx + C::VX - 1) / C::VX);
     p.nty = (int)((ny + C::VY - 1) / C::VY);
     const long long tiles = (long long)p.ntx * p.nty;
-    // pick the chunk count maximising (useful planes / streamed planes) x (wave fill)
-    double best = -1.0;
-    long long best_c = 1;
-    for (long long c = 1; c <= 256 && c <= planes; ++c) {
-        const long long cp = (planes + c - 1) / c;
-        const long long nc = (planes + cp - 1) / cp;
-        const long long blocks = tiles * nc;
-        const long long waves = (blocks + sm_count - 1) / sm_count;
-        const double fill = (double)blocks / (double)(waves * sm_count);
-        const double eff = fill * (double)cp / (double)(cp + 3 * K - 1);
-        if (eff > best + 1e-9) {
-            best = eff;
-            best_c = nc;
-            p.chunk_planes = (int)cp;
+    static std::map<std::array<long long, 6>, std::pair<int, long long>> cache;
+    const std::array<long long, 6> key = {nx, ny, planes, sm_count, K, (long long)sizeof(T)};
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+        const double startup = 3.0;  // CTA launch + first TMA round trip, in plane-steps
+        double best = 1e300;
+        int best_cp = (int)planes;
+        long long best_nc = 1;
+        std::vector<double> heap;
+        for (long long c = 1; c <= 256 && c <= planes; ++c) {
+            const long long cp = (planes + c - 1) / c;
+            const long long nc = (planes + cp - 1) / cp;
+            if (c > 1 && nc == (planes + (planes + c - 2) / (c - 1) - 1) / ((planes + c - 2) / (c - 1)) &&
+                cp == (planes + c - 2) / (c - 1))
+                continue;  // same split as the previous candidate
+            const double dfull = cp + 3 * K - 1 + startup;
+            const double dlast = (planes - (nc - 1) * cp) + 3 * K - 1 + startup;
+            // min-heap of SM free times
+            heap.assign((size_t)sm_count, 0.0);
+            auto push_cta = [&](double d) {
+                std::pop_heap(heap.begin(), heap.end(), std::greater<double>());
+                heap.back() += d;
+                std::push_heap(heap.begin(), heap.end(), std::greater<double>());
+            };
+            for (long long ch = 0; ch < nc; ++ch)
+                for (long long i = 0; i < tiles; ++i) push_cta(ch + 1 < nc ? dfull : dlast);
+            const double makespan = *std::max_element(heap.begin(), heap.end());
+            if (makespan < best - 1e-9) {
+                best = makespan;
+                best_cp = (int)cp;
+                best_nc = nc;
+            }
         }
+        if (cache.size() > 256) cache.clear();
+        it = cache.emplace(key, std::make_pair(best_cp, best_nc)).first;
     }
-    p.nchunks = best_c;
+    p.chunk_planes = it->second.first;
+    p.nchunks = it->second.second;
     p.blocks = tiles * p.nchunks;
     return p;
 }

@@ -5,6 +5,12 @@ The reference decomposes its grid over an 8x8 core mesh and exchanges halos ever
 rank g owns a contiguous slab of planes plus `ghost = radius * k` ghost planes per
 internal face, exchanged once per fused block of k time steps:
 
+  exchange="p2p" (default for the 3-D radius-1 family): ONE launch per block; its face
+    CTAs run first and store their planes straight into the neighbours' ghost planes over
+    NVLink (CUDA IPC peer mappings), signalling arrival counters the neighbours' next launch
+    acquires — no NCCL call, no extra launch, no host sync on the data path
+    (csrc/tma3d.cuh: SlabLinkDev).
+  exchange="nccl" (2-D grids, generic kernel, and the measured baseline):
     faces first (side stream)  ->  send/recv face planes (NCCL, NVLink)   \
     interior planes (main stream, concurrently)                             -> join
 
@@ -41,7 +47,7 @@ def resolve_kernel(desc: capi.Desc):
 class CudaEngine:
     """Device buffers + kernels through the C ABI (the product path)."""
 
-    def __init__(self, desc: capi.Desc, ghost: int, device_index: int):
+    def __init__(self, desc: capi.Desc, ghost: int, device_index: int, exportable: bool = False):
         import torch
         self.torch = torch
         self.desc, self.ghost = desc, ghost
@@ -49,6 +55,14 @@ class CudaEngine:
         self.lay = capi.layout_for(desc, ghost)
         self.np_dtype = torch.float64 if desc.dtype == capi.F64 else torch.float32
         es = 8 if desc.dtype == capi.F64 else 4
+        self.exportable = exportable
+        self.link = None
+        if exportable:
+            # cudaMalloc'ed by the library so the buffers can be IPC-exported to the neighbours
+            self.raw = [_LibBuffer(self.lay.bytes) for _ in range(2)]
+            self.flags = _LibBuffer(4 * capi.LINK_FLAG_WORDS)
+            self.side = torch.cuda.Stream(self.device, priority=-1)
+            return
         self.raw = [torch.zeros(self.lay.bytes, dtype=torch.uint8, device=self.device) for _ in range(2)]
         if desc.ndim == 3:
             shp = (self.lay.planes, self.lay.pitch_y, self.lay.pitch_x)
@@ -93,6 +107,70 @@ class CudaEngine:
             self._st(), ctypes.byref(out)))
         return out.value
 
+    # -- peer link (exchange="p2p") ---------------------------------------------------
+    def connect(self, rank: int, world: int, dist) -> None:
+        """Exchange CUDA IPC handles of both grids + the flag block with all ranks and map
+        the two neighbours' memory."""
+        torch, L = self.torch, capi.lib()
+        hb = capi.IPC_HANDLE_BYTES
+        mine = bytearray()
+        for buf in (self.raw[0], self.raw[1], self.flags):
+            h = ctypes.create_string_buffer(hb)
+            capi.check(L.sb200_ipc_export(buf.data_ptr(), h))
+            mine += h.raw
+        t = torch.tensor(list(mine), dtype=torch.uint8, device=self.device)
+        allh = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allh, t)
+
+        def open_rank(r):
+            if r < 0 or r >= world:
+                return [None, None, None]
+            raw = bytes(allh[r].cpu().tolist())
+            ptrs = []
+            for i in range(3):
+                p = ctypes.c_void_p()
+                capi.check(L.sb200_ipc_open(raw[i * hb:(i + 1) * hb], ctypes.byref(p)))
+                ptrs.append(p.value)
+            return ptrs
+        self.peer_lo, self.peer_hi = open_rank(rank - 1), open_rank(rank + 1)
+        self.arrivals = 0
+        self.link = capi.SlabLink()
+
+    def sweep_linked(self, src, dst, steps, lo_b, hi_b) -> int:
+        lk = self.link
+        lk.peer_dst_lo, lk.peer_dst_hi = self.peer_lo[dst], self.peer_hi[dst]
+        lk.flags_local = self.flags.data_ptr()
+        lk.flags_lo, lk.flags_hi = self.peer_lo[2], self.peer_hi[2]
+        lk.wait_arrivals = self.arrivals & 0xFFFFFFFF
+        arr = ctypes.c_uint32(0)
+        capi.check(capi.lib().sb200_sweep_slab_linked(
+            ctypes.byref(self.desc), self.ghost, lo_b, hi_b, self.raw[src].data_ptr(),
+            self.raw[dst].data_ptr(), steps, ctypes.byref(lk), self._st(), ctypes.byref(arr)))
+        self.arrivals += arr.value
+        return 1
+
+    def link_timed_out(self) -> bool:
+        """True if any face CTA gave up waiting for a neighbour (results are then invalid)."""
+        words = (ctypes.c_uint32 * capi.LINK_FLAG_WORDS)()
+        capi.check(capi.lib().sb200_link_status(self.flags.data_ptr(), words))
+        return words[2] != 0
+
+    def close_peers(self):
+        if self.exportable and self.link is not None:
+            for ptrs in (self.peer_lo, self.peer_hi):
+                for p in ptrs:
+                    if p:
+                        capi.check(capi.lib().sb200_ipc_close(p))
+            self.peer_lo = self.peer_hi = [None, None, None]
+            self.link = None
+
+    def free(self):
+        self.raw = []
+        self.flags = None
+
+    def sync(self):
+        self.torch.cuda.synchronize(self.device)
+
     # stream plumbing used by SlabSweep
     def side_stream(self):
         return self.side
@@ -107,11 +185,31 @@ class CudaEngine:
         return self.torch.cuda.stream(stream)
 
 
+class _LibBuffer:
+    """Zero-filled device memory owned by the library (cudaMalloc: IPC-exportable)."""
+
+    def __init__(self, nbytes: int):
+        p = ctypes.c_void_p()
+        capi.check(capi.lib().sb200_device_alloc(ctypes.byref(p), nbytes))
+        self.ptr, self.nbytes = p.value, nbytes
+
+    def data_ptr(self) -> int:
+        return self.ptr
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                capi.lib().sb200_device_free(self.ptr)
+                self.ptr = None
+        except Exception:  # noqa: BLE001  (interpreter shutdown)
+            pass
+
+
 class SlabSweep:
     """T double-buffered steps of `desc` (the per-rank slab) across `world` ranks."""
 
     def __init__(self, desc: capi.Desc, rank: int = 0, world: int = 1, engine_factory=None,
-                 dist=None):
+                 dist=None, exchange: str = "auto"):
         self.desc, self.rank, self.world = desc, rank, world
         self.kernel, self.time_block = resolve_kernel(desc)
         self.kernel_name = _KERNEL_NAMES[self.kernel]
@@ -123,25 +221,53 @@ class SlabSweep:
         if world > 1 and self.n_outer < 2 * self.ghost:
             raise ValueError(f"slab of {self.n_outer} planes is thinner than two ghost zones "
                              f"({self.ghost} each); use fewer ranks or a smaller time block")
-        factory = engine_factory or (lambda d, g: CudaEngine(d, g, _current_device()))
+        if exchange == "auto":
+            exchange = "p2p" if (world > 1 and self.kernel == capi.KERNEL_TMA3D) else "nccl"
+        if exchange not in ("p2p", "nccl"):
+            raise ValueError(f"exchange must be 'auto', 'p2p' or 'nccl' (got {exchange!r})")
+        if exchange == "p2p" and self.kernel != capi.KERNEL_TMA3D:
+            raise ValueError("exchange='p2p' needs the 3-D radius-1 kernel family")
+        self.exchange = exchange if world > 1 else "none"
+        p2p = self.exchange == "p2p"
+        factory = engine_factory or (lambda d, g: CudaEngine(d, g, _current_device(), exportable=p2p))
         self.eng = factory(desc, self.ghost)
         self.cur = 0
         self.lo_b = 1 if rank == 0 else 0
         self.hi_b = 1 if rank == world - 1 else 0
-        self.kernels_per_launch_unit = 1 if world == 1 else (1 + (not self.lo_b) + (not self.hi_b))
+        self.kernels_per_launch_unit = 1 if (world == 1 or p2p) else (1 + (not self.lo_b) + (not self.hi_b))
         if world > 1:
             if dist is None:
                 import torch.distributed as dist  # noqa: PLC0415
             self.dist = dist
+            if p2p:
+                self.eng.connect(rank, world, dist)
 
     # -- setup ----------------------------------------------------------------------
+    def _quiesce(self):
+        """p2p: neighbours write into this rank's ghost planes from inside their kernels, so
+        host-side buffer writes (fill) must be fenced by device sync + barrier on both sides."""
+        if self.exchange == "p2p":
+            self.eng.sync()
+            self.dist.barrier()
+
     def fill(self, init=capi.INIT_REF, seed=0):
         off, tot = self.rank * self.n_outer, self.n_outer * self.world
         if self.world == 1:
             off = tot = 0
+        self._quiesce()
         self.eng.fill(0, init, seed, off, tot)
         self.eng.fill(1, capi.INIT_REF, 0, off, tot)
         self.cur = 0
+        self._quiesce()
+
+    def close(self):
+        """p2p: unmap the neighbours' memory on every rank BEFORE any rank frees its grids."""
+        if self.exchange == "p2p" and self.eng is not None:
+            self._quiesce()
+            self.eng.close_peers()
+            self.dist.barrier()
+            self.eng.free()
+        self.eng = None
 
     def checksum(self) -> int:
         off, tot = self.rank * self.n_outer, self.n_outer * self.world
@@ -177,6 +303,11 @@ class SlabSweep:
         return launches
 
     def _block(self, k: int) -> int:
+        if self.exchange == "p2p":
+            dst = self.cur ^ 1
+            nl = self.eng.sweep_linked(self.cur, dst, k, self.lo_b, self.hi_b)
+            self.cur = dst
+            return nl
         # faces are always `ghost` deep (also for a shorter remainder block) so that every
         # ghost plane is refreshed to the new time level by each exchange
         eng, n, g = self.eng, self.n_outer, self.ghost

@@ -81,6 +81,28 @@ class OracleEngine:
         out[inner] = res[zb - lo + r:ze - lo + r][inner]
         return 1
 
+    # exchange="p2p" stand-in: one "launch" sweeps the whole slab, then the face planes land
+    # in the neighbours' ghost planes (the CUDA engine does this with peer stores + flags)
+    def connect(self, rank, world, dist_):
+        self.rank, self.world, self.dist = rank, world, dist_
+
+    def sync(self):
+        pass
+
+    def sweep_linked(self, src, dst, steps, lo_b, hi_b):
+        n, g = self.n[-1], self.ghost
+        self.sweep_range(src, dst, steps, 0, n, lo_b, hi_b)
+        ops = []
+        if not lo_b:
+            ops.append(self.dist.P2POp(self.dist.isend, self.planes(dst, 0, g).contiguous(), self.rank - 1))
+            ops.append(self.dist.P2POp(self.dist.irecv, self.planes(dst, -g, 0), self.rank - 1))
+        if not hi_b:
+            ops.append(self.dist.P2POp(self.dist.isend, self.planes(dst, n - g, n).contiguous(), self.rank + 1))
+            ops.append(self.dist.P2POp(self.dist.irecv, self.planes(dst, n, n + g), self.rank + 1))
+        for w in self.dist.batch_isend_irecv(ops):
+            w.wait()
+        return 1
+
     def side_stream(self):
         return None
 
@@ -94,7 +116,7 @@ class OracleEngine:
         return _NullCtx()
 
 
-def _worker(rank, world, port, n, shape, dtype, T, k, out):
+def _worker(rank, world, port, n, shape, dtype, T, k, out, exchange="nccl"):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -102,7 +124,8 @@ def _worker(rank, world, port, n, shape, dtype, T, k, out):
         ln = list(n)
         ln[-1] //= world
         d = capi.make_desc(ln, 1, shape, dtype, T, time_block=k)
-        sw = slab.SlabSweep(d, rank, world, engine_factory=OracleEngine, dist=dist)
+        sw = slab.SlabSweep(d, rank, world, engine_factory=OracleEngine, dist=dist, exchange=exchange)
+        assert sw.exchange == exchange
         sw.fill(capi.INIT_RANDOM, seed=4)
         nl = sw.sweep(T)
         res = sw.eng.planes(sw.cur, 0, ln[-1]).clone()
@@ -129,6 +152,27 @@ def test_slab_exchange_matches_single_grid(tmp_path, world, n, shape, dtype, T, 
     want = oracle.run(n, 1, oracle.STAR if shape == capi.STAR else oracle.BOX, T, code,
                       oracle.INIT_RANDOM, 4)
     assert np.array_equal(got.view(np.uint8), want[1:-1].view(np.uint8))
+
+
+@pytest.mark.parametrize("world,n,T,k", [(2, (20, 12, 16), 5, 2), (3, (10, 9, 18), 7, 3)])
+def test_slab_linked_flow_matches_single_grid(tmp_path, world, n, T, k):
+    """exchange="p2p": one linked launch per fused block, remainder block included."""
+    out = str(tmp_path / "res.npy")
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_worker, args=(world, port, n, capi.STAR, capi.F64, T, k, out, "p2p"), nprocs=world, join=True)
+    got = np.load(out)
+    want = oracle.run(n, 1, oracle.STAR, T, oracle.F64, oracle.INIT_RANDOM, 4)
+    assert np.array_equal(got.view(np.uint8), want[1:-1].view(np.uint8))
+
+
+def test_exchange_mode_selection():
+    d3 = capi.make_desc((8, 8, 8), time_block=2)
+    d2 = capi.make_desc((8, 8), shape=capi.BOX)
+    assert slab.SlabSweep(d3, 0, 1, engine_factory=OracleEngine).exchange == "none"
+    with pytest.raises(ValueError):
+        slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
+    with pytest.raises(ValueError):
+        slab.SlabSweep(d3, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="bogus")
 
 
 def test_resolve_kernel_defaults():

@@ -23,6 +23,7 @@ ap.add_argument("--mode", default="strong")
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--time-block", type=int, default=0)
+ap.add_argument("--exchange", default="auto")
 ap.add_argument("--nz", type=int, default=2048)
 ap.add_argument("--nxy", type=int, default=1024)
 args = ap.parse_args()
@@ -34,7 +35,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 nz_local = args.nz // world if args.mode == "strong" else 256
 d = capi.make_desc((args.nxy, args.nxy, nz_local), 1, capi.STAR, capi.F64, args.steps, time_block=args.time_block)
-sw = slab.SlabSweep(d, rank, world)
+sw = slab.SlabSweep(d, rank, world, exchange=args.exchange)
 
 
 def barrier():
@@ -66,7 +67,8 @@ pts = args.nxy * args.nxy * nz_local * world
 if rank == 0:
     gs = pts * args.steps / best / 1e6
     print(json.dumps({"config": 5, "mode": args.mode, "n_gpus": world, "grid_zyx": [nz_local * world, args.nxy, args.nxy],
-                      "steps": args.steps, "time_block": sw.time_block, "ms": best, "GStencil/s": gs,
+                      "steps": args.steps, "time_block": sw.time_block, "exchange": sw.exchange, "ms": best, "GStencil/s": gs,
                       "alg_GBps_per_gpu": gs * 16 / world, "checksum": f"{total:#018x}"}), flush=True)
+sw.close()
 if world > 1:
     dist.destroy_process_group()

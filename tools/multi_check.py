@@ -15,14 +15,20 @@ torch.cuda.set_device(local)
 capi.check(capi.lib().sb200_init(local))
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for n_local, shape, dtype, T, k in [((256, 200, 64), capi.STAR, capi.F64, 7, 2),
-                                     ((256, 200, 64), capi.STAR, capi.F32, 6, 3),
-                                     ((1000, 256), capi.BOX, capi.F32, 19, 4),
-                                     ((300, 128, 40), capi.BOX, capi.F64, 3, 1)]:
+for n_local, shape, dtype, T, k, exch in [((256, 200, 64), capi.STAR, capi.F64, 7, 2, "p2p"),
+                                           ((256, 200, 64), capi.STAR, capi.F64, 7, 2, "nccl"),
+                                           ((256, 200, 64), capi.STAR, capi.F32, 6, 3, "p2p"),
+                                           ((130, 61, 12), capi.STAR, capi.F64, 31, 2, "p2p"),
+                                           ((1000, 256), capi.BOX, capi.F32, 19, 4, "nccl"),
+                                           ((300, 128, 40), capi.BOX, capi.F64, 3, 1, "nccl"),
+                                           ((300, 128, 40), capi.BOX, capi.F64, 9, 2, "p2p")]:
     d = capi.make_desc(n_local, 1, shape, dtype, T, time_block=k)
-    sw = slab.SlabSweep(d, rank, world)
+    sw = slab.SlabSweep(d, rank, world, exchange=exch)
     sw.fill(capi.INIT_RANDOM, seed=3)
     sw.sweep(T)
+    if exch == "p2p" and sw.eng.link_timed_out():
+        print(f"rank {rank}: a face CTA timed out waiting for its neighbour", flush=True)
+        ok = False
     cs = torch.tensor([sw.checksum() & 0x7FFFFFFFFFFFFFFF, sw.checksum() >> 63], dtype=torch.int64, device="cuda")
     parts = [torch.zeros_like(cs) for _ in range(world)]
     dist.all_gather(parts, cs)
@@ -37,9 +43,13 @@ for n_local, shape, dtype, T, k in [((256, 200, 64), capi.STAR, capi.F64, 7, 2),
         want = g.checksum()
         good = want == total
         ok &= good
-        print(f"n_local={n_local} shape={shape} dtype={dtype} T={T} k={k} world={world}: "
+        print(f"n_local={n_local} shape={shape} dtype={dtype} T={T} k={k} world={world} exchange={exch}: "
               f"{'bitwise identical' if good else 'MISMATCH'} ({want:#x} vs {total:#x})", flush=True)
         del g
     dist.barrier()
+    sw.close()
+okt = torch.tensor([1 if ok else 0], device="cuda")
+dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+ok = bool(okt.item())
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)
