@@ -256,17 +256,30 @@ struct W2dPlan {
     long long nchunks, nitems;
 };
 
+// Rows per chunk.  Large grids: ~2 rounds of 16 warps per SM with chunks of at least 16K
+// rows, so the 2K redundant rows per chunk stay a small fraction (HBM-bound regime).  Small
+// grids — the reference's own N <= 960 regime (run_expr.py:6-14) — cannot fill the machine
+// that way and a launch costs the latency of ONE warp walking its chunk row by row, so they
+// are cut into short chunks (>= 4 rows) until every SM sub-partition has a few warps.
 static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count) {
     W2dPlan p;
     const int V = (W2D_WIDTH - ((K + 3) & ~3) - K) & ~3;
     p.nstrips = (int)((nx + V - 1) / V);
-    // enough warps to fill the machine (~16 resident warps per SM, 2 rounds), but chunks
-    // of at least 16*K rows so the 2K redundant rows per chunk stay a small fraction
     const long long want_items = (long long)sm_count * 16 * 2;
     long long nchunks = (want_items + p.nstrips - 1) / p.nstrips;
-    long long min_rows = 16LL * K;
     long long chunk_rows = (rows + nchunks - 1) / nchunks;
-    if (chunk_rows < min_rows) chunk_rows = min_rows;
+    const long long min_rows = 16LL * K;
+    const bool small = ((rows + min_rows - 1) / min_rows) * p.nstrips < (long long)sm_count * 8;
+    if (chunk_rows < min_rows && !small) chunk_rows = min_rows;
+    if (chunk_rows < min_rows && small) {
+        // latency-bound regime: warps per sub-partition that still overlap (fewer for deep K,
+        // whose row step is issue-heavy)
+        const int per_smsp = K <= 2 ? 4 : (K <= 4 ? 2 : 1);
+        const long long target = (long long)sm_count * 4 * per_smsp;
+        nchunks = (target + p.nstrips - 1) / p.nstrips;
+        chunk_rows = (rows + nchunks - 1) / nchunks;
+        if (chunk_rows < 4) chunk_rows = 4;
+    }
     if (chunk_rows > rows) chunk_rows = rows;
     if (chunk_rows < 1) chunk_rows = 1;
     p.chunk_rows = (int)chunk_rows;
