@@ -43,7 +43,12 @@ typedef enum sb200_kernel {
     SB200_KERNEL_AUTO = 0,
     SB200_KERNEL_GENERIC = 1, /* one step per launch, any ndim/shape/radius   */
     SB200_KERNEL_WARP2D = 2,  /* 2-D r=1, register/shuffle temporal blocking   */
-    SB200_KERNEL_TMA3D = 3    /* 3-D r=1, TMA-staged z-streaming, temporal blk */
+    SB200_KERNEL_TMA3D = 3,   /* 3-D r=1, TMA-staged z-streaming, temporal blk */
+    SB200_KERNEL_RESIDENT2D = 4 /* small 2-D r=1 grids: register-resident in one
+                                   thread-block cluster for ALL steps of a call, one
+                                   launch (the analogue of the reference's RMA kernel,
+                                   stencil_rma.cpp:333-458); AUTO picks it for
+                                   single-GPU calls of >= 16 steps when the grid fits */
 } sb200_kernel;
 
 /* Problem descriptor.  Replaces the reference's `Arguments{block_size,

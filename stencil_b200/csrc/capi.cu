@@ -16,6 +16,7 @@
 #include "../../include/stencil_b200.h"
 #include "common.cuh"
 #include "generic.cuh"
+#include "resident2d_api.h"
 #include "tma3d.cuh"
 #include "util_kernels.cuh"
 #include "warp2d.cuh"
@@ -84,7 +85,7 @@ int validate(const sb200_desc* d) {
         if (a >= d->ndim && d->n[a] > 1) return fail(SB200_ERR_INVALID, "n[%d] must be 1 for ndim=%d", a, d->ndim);
         if (d->n[a] > (1ull << 40)) return fail(SB200_ERR_INVALID, "n[%d] too large", a);
     }
-    if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_TMA3D)
+    if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_RESIDENT2D)
         return fail(SB200_ERR_INVALID, "bad kernel selector %d", d->kernel);
     return SB200_OK;
 }
@@ -231,8 +232,10 @@ Choice choose(const sb200_desc* d) {
         kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : SB200_KERNEL_GENERIC;
     c.kernel = kern;
     c.max_k = kern == SB200_KERNEL_WARP2D ? W2D_MAXK
-              : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK) : 1;
+              : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
+              : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30) : 1;
     int k = (int)d->time_block;
+    if (kern == SB200_KERNEL_RESIDENT2D) k = c.max_k;  // the whole call is one launch
     if (k == 0) k = kern == SB200_KERNEL_WARP2D ? 4 : kern == SB200_KERNEL_TMA3D ? 2 : 1;
     if (k > c.max_k) k = c.max_k;
     c.k = k;
@@ -244,6 +247,10 @@ int check_choice(const sb200_desc* d, const Choice& c) {
         return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2, radius=1");
     if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
         return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1");
+    if (c.kernel == SB200_KERNEL_RESIDENT2D &&
+        !(d->ndim == 2 && d->radius == 1 && resident2d_fits((long long)d->n[0], (long long)d->n[1], (int)esize(d->dtype))))
+        return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel needs ndim=2, radius=1 and a grid that fits one "
+                                           "thread-block cluster's registers (about 672^2 fp32 / 512^2 fp64)");
     return SB200_OK;
 }
 
@@ -262,7 +269,7 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
         case SB200_KERNEL_TMA3D:
             return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
     }
-    return fail(SB200_ERR_INVALID, "bad kernel");
+    return fail(SB200_ERR_INVALID, "kernel family %d cannot run a partial pass", c.kernel);
 }
 
 int pass(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, const void* a, void* b,
@@ -285,11 +292,26 @@ Domain make_domain(const Grid& g, int lo_b, int hi_b) {
 int sweep_impl(const sb200_desc* d, uint32_t ghost, int lo_b, int hi_b, void* a, void* b,
                uint32_t steps, cudaStream_t st, int* result_in_b, uint32_t* launches,
                uint32_t* used_k, int* used_kernel) {
-    const Choice c = choose(d);
+    Choice c = choose(d);
     if (int rc = check_choice(d, c)) return rc;
     const Grid g = make_grid(d, ghost);
     if (d->ndim == 1 && ghost) return fail(SB200_ERR_INVALID, "1-D grids cannot carry ghost cells");
     const int r = (int)d->radius;
+    // Small 2-D grids, single GPU, many steps: keep the grid on chip for the whole call.
+    const bool whole = ghost == 0 && lo_b && hi_b;
+    bool resident = c.kernel == SB200_KERNEL_RESIDENT2D;
+    if (resident && !whole) return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel cannot sweep a slab with ghost planes");
+    if (d->kernel == SB200_KERNEL_AUTO && d->time_block == 0 && c.kernel == SB200_KERNEL_WARP2D && whole &&
+        steps >= 16 && resident2d_fits(g.n[0], g.n[1], (int)esize(d->dtype)))
+        resident = true;
+    if (resident) {
+        if (steps > 0) CU_TRY(launch_resident2d(a, b, g, d->shape, (int)esize(d->dtype), (int)steps, st));
+        if (result_in_b) *result_in_b = steps > 0 ? 1 : 0;
+        if (launches) *launches = steps > 0 ? 1 : 0;
+        if (used_k) *used_k = steps;
+        if (used_kernel) *used_kernel = SB200_KERNEL_RESIDENT2D;
+        return SB200_OK;
+    }
     if ((!lo_b || !hi_b) && (long long)steps * r > (long long)ghost)
         return fail(SB200_ERR_INVALID, "%u steps of radius %d need %lld ghost planes, have %u", steps, r,
                     (long long)steps * r, ghost);
@@ -400,6 +422,8 @@ int sb200_sweep_device_range(const sb200_desc* desc, uint32_t ghost, int lo_is_b
     if (int rc = ensure_ready()) return rc;
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
+    if (c.kernel == SB200_KERNEL_RESIDENT2D)
+        return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel sweeps whole grids only");
     if (steps < 1 || (int)steps > c.max_k)
         return fail(SB200_ERR_INVALID, "range sweep fuses 1..%d steps (got %u)", c.max_k, steps);
     if (desc->ndim == 1) return fail(SB200_ERR_INVALID, "range sweep needs ndim >= 2");

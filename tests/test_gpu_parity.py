@@ -137,3 +137,33 @@ def test_device_api_fill_checksum_matches_oracle(gpu, n, shape, dtype, k):
     g.sweep(T)
     assert g.checksum() == oracle.checksum(n, 1, want)
     assert np.array_equal(g.download().view(np.uint8), want.view(np.uint8))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
+@pytest.mark.parametrize("n,T", [
+    ((1, 1), 3), ((3, 2), 5), ((64, 64), 16), ((64, 64), 101), ((130, 70), 33), ((129, 5), 7),
+    ((300, 200), 24), ((400, 400), 40), ((512, 512), 18), ((1000, 60), 9), ((127, 511), 12),
+])
+def test_resident2d_kernel(gpu, n, T, shape, dtype):
+    """Register-resident cluster kernel (1..16 CTAs, DSMEM edge exchange): one launch for all
+    T steps, bit-exact against the oracle; T parity still selects the host buffer."""
+    t = _check(n, 1, shape, dtype, T, kernel=capi.KERNEL_RESIDENT2D)
+    assert t.kernel == capi.KERNEL_RESIDENT2D and t.launches == 1
+
+
+def test_resident2d_auto_and_limits(gpu):
+    # AUTO keeps small many-step 2-D grids on chip, and falls back to warp2d otherwise
+    t = _check((400, 400), 1, capi.STAR, np.float32, 64)
+    assert t.kernel == capi.KERNEL_RESIDENT2D and t.launches == 1
+    t = _check((400, 400), 1, capi.STAR, np.float32, 8)
+    assert t.kernel == capi.KERNEL_WARP2D
+    t = _check((576, 576), 1, capi.BOX, np.float32, 20)
+    assert t.kernel == capi.KERNEL_RESIDENT2D
+    t = _check((640, 640), 1, capi.BOX, np.float32, 20)
+    assert t.kernel == capi.KERNEL_WARP2D
+    t = _check((1000, 900), 1, capi.STAR, np.float32, 20)
+    assert t.kernel == capi.KERNEL_WARP2D
+    a, b = _oracle_pair((1000, 900), 1, np.float32, 1)
+    with pytest.raises(capi.StencilError):
+        sweep.run_host((1000, 900), a, b, 4, kernel=capi.KERNEL_RESIDENT2D)

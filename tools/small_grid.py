@@ -11,7 +11,7 @@ from stencil_b200 import capi, sweep
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 10000
 capi.check(capi.lib().sb200_init(0))
 for N in (64, 128, 256, 384, 400, 512, 640, 800, 960):
-    for k in (0, 8):
+    for k in (0, 4, 8):  # 0 = AUTO (register-resident cluster kernel when the grid fits)
         d = capi.make_desc((N, N), 1, capi.STAR, capi.F32, T, time_block=k)
         g = sweep.DeviceGrids(d)
         g.fill(capi.INIT_RANDOM, seed=1)
