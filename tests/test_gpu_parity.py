@@ -167,3 +167,56 @@ def test_resident2d_auto_and_limits(gpu):
     a, b = _oracle_pair((1000, 900), 1, np.float32, 1)
     with pytest.raises(capi.StencilError):
         sweep.run_host((1000, 900), a, b, 4, kernel=capi.KERNEL_RESIDENT2D)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
+@pytest.mark.parametrize("n,T,k", [((70, 66, 12), 4, 2), ((130, 61, 9), 5, 2), ((64, 64, 40), 3, 1)])
+def test_slab_link_self_periodic(gpu, n, T, k, shape, dtype):
+    """The fused halo exchange (sb200_sweep_slab_linked: peer stores + arrival counters) on
+    ONE GPU: the slab is its own lower and upper neighbour, i.e. periodic in z.  For T <= nz
+    that equals the middle copy of three stacked copies swept with the ordinary Dirichlet
+    oracle, bit for bit."""
+    import torch
+    nx, ny, nz = n
+    g = k  # ghost planes = radius * fused depth
+    assert T <= nz
+    code = oracle.F64 if dtype == np.float64 else oracle.F32
+    P = oracle.fill(n, 1, code, oracle.INIT_RANDOM, 11)
+    n3 = (nx, ny, 3 * nz)
+    A3, B3 = oracle.fill(n3, 1, code, oracle.INIT_REF), oracle.fill(n3, 1, code, oracle.INIT_REF)
+    for c in range(3):
+        A3[1 + c * nz:1 + (c + 1) * nz] = P[1:-1]
+    want3 = B3 if oracle.sweep(n3, 1, shape, T, A3, B3, threads=oracle.max_threads()) else A3
+    want = want3[1 + nz:1 + 2 * nz, 1:-1, 1:-1]
+
+    d = capi.make_desc(n, 1, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
+    dg = sweep.DeviceGrids(d, ghost=g)
+    S = np.empty((nz + 2 * (1 + g), ny + 2, nx + 2), dtype)
+    for p in range(S.shape[0]):
+        S[p] = P[1 + (p - (1 + g)) % nz]
+    dg.upload(S, 0)
+    dg.upload(S, 1)
+    flags = torch.zeros(capi.LINK_FLAG_WORDS, dtype=torch.int32, device="cuda")
+    L, arrivals, cur, done = capi.lib(), 0, 0, 0
+    bufs = (dg.a, dg.b)
+    while done < T:
+        kk = min(k, T - done)
+        lk = capi.SlabLink()
+        lk.peer_dst_lo = lk.peer_dst_hi = bufs[cur ^ 1].data_ptr()
+        lk.flags_local = lk.flags_lo = lk.flags_hi = flags.data_ptr()
+        lk.wait_arrivals = arrivals
+        arr = ctypes.c_uint32(0)
+        capi.check(L.sb200_sweep_slab_linked(ctypes.byref(d), g, 0, 0, bufs[cur].data_ptr(),
+                                             bufs[cur ^ 1].data_ptr(), kk, ctypes.byref(lk),
+                                             dg._stream(), ctypes.byref(arr)))
+        assert arr.value > 0
+        arrivals += arr.value
+        cur ^= 1
+        done += kk
+    words = (ctypes.c_uint32 * capi.LINK_FLAG_WORDS)()
+    capi.check(L.sb200_link_status(flags.data_ptr(), words))
+    assert words[2] == 0, "a face CTA timed out waiting for its neighbour"
+    assert words[0] == arrivals and words[1] == arrivals
+    got = dg.download(cur)[1 + g:1 + g + nz, 1:-1, 1:-1]
+    assert np.array_equal(got.view(np.uint8), np.ascontiguousarray(want).view(np.uint8))
