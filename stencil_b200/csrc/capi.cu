@@ -187,10 +187,10 @@ int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, lo
         if (nc < 1) nc = 1;
         link.nchunks = (int)nc;
         sweep_tma3d_kernel<T, K, SHAPE, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
-            *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
+            *map, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
     } else {
         sweep_tma3d_kernel<T, K, SHAPE, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
-            *map, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link_in);
+            *map, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link_in);
     }
     CU_TRY(cudaGetLastError());
     return SB200_OK;

@@ -257,9 +257,9 @@ __device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsi
 
 template <class T, int K, int SHAPE, bool LINKED>
 __global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
-sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out, Grid g,
-                   Domain dom, long long ob, long long oe, int ntx, int nty, int chunk_planes,
-                   T avg, const SlabLinkDev link) {
+sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict__ in,
+                   T* __restrict__ out, Grid g, Domain dom, long long ob, long long oe, int ntx, int nty,
+                   int chunk_planes, T avg, const SlabLinkDev link) {
     using C = T3<T, K>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
     static_assert((S & (S - 1)) == 0 && S >= 2, "stage count must be a power of two");
@@ -409,9 +409,14 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, T* __restrict__ out
             VecN<T, PXV>::st(wb, o[0]);
             VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
         } else {
+            // The last level needs no pass-through fix-up: only updatable points of planes
+            // inside the update domain are ever stored.  The box variant drops it (and with it
+            // the register history of the previous plane, which only the fix-up reads: no
+            // spills at K=2); the star variant carries that history anyway for its
+            // arithmetic and keeps the fix-up — without it ptxas spills inside the plane loop.
             T o[PY][PXV];
             t3_level<T, PXV, PY>(up, c, dn, cm1, lv[L], avg, o);
-            if (!(upd && warp_all)) {
+            if (SHAPE == STAR && !(upd && warp_all)) {
                 const unsigned m = upd ? mask : 0u;
 #pragma unroll
                 for (int i = 0; i < PY; ++i)
