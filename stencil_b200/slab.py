@@ -113,14 +113,20 @@ class CudaEngine:
         the two neighbours' memory."""
         torch, L = self.torch, capi.lib()
         hb = capi.IPC_HANDLE_BYTES
-        mine = bytearray()
-        for buf in (self.raw[0], self.raw[1], self.flags):
-            h = ctypes.create_string_buffer(hb)
-            capi.check(L.sb200_ipc_export(buf.data_ptr(), h))
-            mine += h.raw
+        mine, export_err = bytearray(), None
+        try:
+            for buf in (self.raw[0], self.raw[1], self.flags):
+                h = ctypes.create_string_buffer(hb)
+                capi.check(L.sb200_ipc_export(buf.data_ptr(), h))
+                mine += h.raw
+        except capi.StencilError as e:
+            export_err, mine = e, bytearray(3 * hb)
+        # every rank takes part in the collective even if its export failed
         t = torch.tensor(list(mine), dtype=torch.uint8, device=self.device)
         allh = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(allh, t)
+        if export_err is not None:
+            raise export_err
 
         def open_rank(r):
             if r < 0 or r >= world:
@@ -221,7 +227,8 @@ class SlabSweep:
         if world > 1 and self.n_outer < 2 * self.ghost:
             raise ValueError(f"slab of {self.n_outer} planes is thinner than two ghost zones "
                              f"({self.ghost} each); use fewer ranks or a smaller time block")
-        if exchange == "auto":
+        auto = exchange == "auto"
+        if auto:
             exchange = "p2p" if (world > 1 and self.kernel == capi.KERNEL_TMA3D) else "nccl"
         if exchange not in ("p2p", "nccl"):
             raise ValueError(f"exchange must be 'auto', 'p2p' or 'nccl' (got {exchange!r})")
@@ -240,7 +247,33 @@ class SlabSweep:
                 import torch.distributed as dist  # noqa: PLC0415
             self.dist = dist
             if p2p:
-                self.eng.connect(rank, world, dist)
+                # Peer mapping needs CUDA IPC between the ranks' processes.  If ANY rank cannot
+                # map its neighbours (containers without shared IPC namespaces, GPUs without
+                # peer access) every rank learns it here; exchange="auto" then drops to the
+                # NCCL exchange on the GPU, an explicit exchange="p2p" fails loudly.
+                err = None
+                try:
+                    self.eng.connect(rank, world, dist)
+                except Exception as e:  # noqa: BLE001
+                    err = e
+                if not self._all_ok(err is None):
+                    if not auto:
+                        raise RuntimeError(f"exchange='p2p' unavailable on rank {rank}: {err or 'a peer rank failed'}")
+                    if rank == 0:
+                        print(f"stencil_b200: peer mapping unavailable ({err or 'on a peer rank'}); "
+                              "using the NCCL halo exchange", flush=True)
+                    self.exchange = "nccl"
+                    self.kernels_per_launch_unit = 1 + (not self.lo_b) + (not self.hi_b)
+                    self.eng = (engine_factory or (lambda d, g: CudaEngine(d, g, _current_device())))(desc, self.ghost)
+
+    def _all_ok(self, ok: bool) -> bool:
+        """Logical AND of `ok` over all ranks (engines that are not CUDA-backed skip it)."""
+        torch = getattr(self.eng, "torch", None)
+        if torch is None:
+            return ok
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.eng.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN)
+        return bool(int(t.item()))
 
     # -- setup ----------------------------------------------------------------------
     def _quiesce(self):
