@@ -54,7 +54,7 @@ sweep_generic_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, long
 }
 
 // ---- vectorised variant (compile-time radius 1..4) -------------------------------------
-// Each thread owns one 128-bit vector of consecutive x (4 floats / 2 doubles) of one row.
+// Each thread owns 4 consecutive x (one 128-bit vector of floats, two of doubles) of one row.
 // All loads are aligned 128-bit loads through the read-only path: the x window comes from
 // the 2Q+1 vectors around the thread's own, y/z neighbours from one vector per neighbour
 // row; a block is 32 x 8 threads (128 or 64 x by 8 consecutive rows), so the +-r neighbour
@@ -73,13 +73,15 @@ template <> struct GVec<float> {
     }
 };
 template <> struct GVec<double> {
-    static constexpr int V = 2;
+    static constexpr int V = 4;  // two 128-bit vectors per thread: as many points as the fp32 path
     static __device__ __forceinline__ void ld(const double* p, double* v) {
-        const double2 f = __ldg(reinterpret_cast<const double2*>(p));
-        v[0] = f.x; v[1] = f.y;
+        const double2 a = __ldg(reinterpret_cast<const double2*>(p));
+        const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
     }
     static __device__ __forceinline__ void st(double* p, const double* v) {
-        *reinterpret_cast<double2*>(p) = make_double2(v[0], v[1]);
+        reinterpret_cast<double2*>(p)[0] = make_double2(v[0], v[1]);
+        reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
     }
 };
 
