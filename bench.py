@@ -252,7 +252,9 @@ def main():
         e2e = {"value": pts_rank * world * T_STEPS * e2e_steps / float(dt.item()) / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": lay_host, "d2h_bytes_per_step": N_SIDE ** 3 * 8,
                "steps": e2e_steps, "h2d_ms": tm.h2d_ms, "sweep_ms": tm.sweep_ms, "d2h_ms": tm.d2h_ms,
-               "note": "sb200_run_host on pinned host buffers; each rank runs its own 512^3 grid"}
+               "note": "sb200_run_host on pinned host buffers, each rank its own 512^3 grid; upload, sweep and "
+                       "download overlap (z-t parallelograms on separate streams): h2d_ms = all upload chunks, "
+                       "sweep_ms = the whole device pipeline, d2h_ms = first to last download chunk"}
         for p in hp:
             capi.lib().sb200_host_free(p)
 

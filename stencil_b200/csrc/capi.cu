@@ -10,6 +10,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -69,6 +70,10 @@ struct State {
     size_t buf_bytes = 0;
     unsigned long long* d_acc = nullptr;
     bool attr_set = false;
+    // pipelined host path: dense staging image + copy-in / copy-out streams
+    void* staging = nullptr;
+    size_t staging_bytes = 0;
+    cudaStream_t st_in = nullptr, st_out = nullptr, st_sweep[2] = {nullptr, nullptr};
 } S;
 std::mutex g_mu;
 
@@ -375,6 +380,16 @@ void sb200_finalize(void) {
     S.buf_bytes = 0;
     if (S.d_acc) cudaFree(S.d_acc);
     S.d_acc = nullptr;
+    if (S.staging) cudaFree(S.staging);
+    S.staging = nullptr;
+    S.staging_bytes = 0;
+    if (S.st_in) cudaStreamDestroy(S.st_in);
+    if (S.st_out) cudaStreamDestroy(S.st_out);
+    for (auto& q : S.st_sweep) {
+        if (q) cudaStreamDestroy(q);
+        q = nullptr;
+    }
+    S.st_in = S.st_out = nullptr;
     S.maps.clear();
     S.ready = false;
     S.device = -1;
@@ -605,6 +620,195 @@ static int copy_grid(const sb200_desc* desc, uint32_t ghost, const void* src, vo
     return SB200_OK;
 }
 
+// Device interior -> host interior for the outermost-axis range [ob, oe) (interior coords).
+static int download_interior_range(const sb200_desc* desc, const void* dev, void* host, long long ob,
+                                   long long oe, cudaStream_t st) {
+    if (oe <= ob) return SB200_OK;
+    const Grid g = make_grid(desc, 0);
+    const size_t es = esize(desc->dtype);
+    const long long r = g.r;
+    const long long hx = g.n[0] + 2 * r, hy = g.pitch_y;
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof p);
+    p.srcPtr = make_cudaPitchedPtr(const_cast<void*>(dev), (size_t)g.pitch_x * es, (size_t)g.pitch_x, (size_t)g.pitch_y);
+    p.dstPtr = make_cudaPitchedPtr(host, (size_t)hx * es, (size_t)hx, (size_t)hy);
+    if (g.ndim == 3) {
+        p.srcPos = make_cudaPos((size_t)g.ox * es, (size_t)g.oy, (size_t)(g.oz + ob));
+        p.dstPos = make_cudaPos((size_t)r * es, (size_t)g.oy, (size_t)(g.oz + ob));
+        p.extent = make_cudaExtent((size_t)g.n[0] * es, (size_t)g.n[1], (size_t)(oe - ob));
+    } else {
+        p.srcPos = make_cudaPos((size_t)g.ox * es, (size_t)(g.oy + ob), 0);
+        p.dstPos = make_cudaPos((size_t)r * es, (size_t)(g.oy + ob), 0);
+        p.extent = make_cudaExtent((size_t)g.n[0] * es, (size_t)(oe - ob), 1);
+    }
+    p.kind = cudaMemcpyDeviceToHost;
+    CU_TRY(cudaMemcpy3DAsync(&p, st));
+    return SB200_OK;
+}
+
+// Number of z (y in 2-D) parallelograms of the pipelined host path; 1 = not pipelined.
+static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, size_t dense_bytes) {
+    if (d->ndim < 2 || c.kernel == SB200_KERNEL_RESIDENT2D || d->iterations == 0) return 1;
+    const long long n = outer_n(g);
+    const long long reach = (long long)d->iterations * d->radius;  // planes a parallelogram drifts
+    const long long wmin = 4LL * c.k * d->radius;                  // narrowest final region
+    // the LAST final region must be at least `reach` wide (its parallelogram starts at the
+    // high end of the grid); the others only need to be wider than their halos
+    const long long last = reach > wmin ? reach : wmin;
+    long long cmax = n > last ? (n - last) / wmin + 1 : 1;
+    long long want = 8;
+    if (const char* e = getenv("SB200_PIPELINE_CHUNKS")) want = atoll(e);
+    else if (dense_bytes < (64u << 20)) want = 1;  // small grids: the copies are too short to hide
+    if (want > cmax) want = cmax;
+    if (want > 32) want = 32;
+    return want < 2 ? 1 : (int)want;
+}
+
+// The drop-in call for grids that are worth pipelining: the outermost axis is cut into C
+// parallelograms in (z, t) that lean towards low z by `radius` planes per time step.
+// Parallelogram i only needs the planes below its right edge, so it starts as soon as upload
+// chunk i has landed, and its final region [F_i, F_i+1) is complete — and starts its way
+// back to the host — while the parallelograms to its right are still being swept.  H2D, the
+// sweep and D2H run on three streams; PCIe is used in both directions at once.  The slanted
+// right edge of parallelogram i at time level t stays in the ping-pong buffer of that parity
+// (later blocks of i write strictly below it, because block sizes never decrease), which is
+// exactly the halo parallelogram i+1 needs: no extra storage, same kernels, same bits.
+static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
+                              sb200_timing* timing, int C) {
+    const auto w0 = std::chrono::steady_clock::now();
+    const Grid g = make_grid(desc, 0);
+    const size_t es = esize(desc->dtype);
+    const size_t bytes = (size_t)g.elems() * es;
+    const long long n = outer_n(g), r = g.r, T = desc->iterations;
+    const long long hx = g.n[0] + 2 * r;
+    const long long rows_per_outer = g.ndim == 3 ? g.pitch_y : 1;
+    const long long n_outer_padded = g.ndim == 3 ? g.planes : g.pitch_y;
+    const size_t outer_bytes = (size_t)hx * rows_per_outer * es;  // dense bytes per outer index
+    const size_t dense_bytes = outer_bytes * n_outer_padded;
+    if (S.staging_bytes < dense_bytes) {
+        if (S.staging) cudaFree(S.staging);
+        S.staging = nullptr;
+        S.staging_bytes = 0;
+        CU_TRY(cudaMalloc(&S.staging, dense_bytes));
+        S.staging_bytes = dense_bytes;
+    }
+    if (!S.st_in) {
+        CU_TRY(cudaStreamCreateWithFlags(&S.st_in, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&S.st_out, cudaStreamNonBlocking));
+        for (auto& q : S.st_sweep) CU_TRY(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
+    }
+    cudaStream_t st = 0;  // the caller's stream: start / end of the whole pipeline
+    // final regions F_i (equal download chunks) and starting edges Z_i = F_i + T*r
+    std::vector<long long> F(C + 1), Z(C + 1);
+    // final regions: the last one is `reach` (>= 4k*r) wide, the others split the rest evenly
+    {
+        const long long wmin = 4LL * c.k * r;
+        long long last = T * r > wmin ? T * r : wmin;
+        if (const char* e = getenv("SB200_PIPELINE_LAST")) last = atoll(e) > last ? atoll(e) : last;
+        F[0] = 0;
+        for (int i = 1; i < C; ++i) F[i] = (n - last) * i / (C - 1);
+        F[C] = n;
+    }
+    Z[0] = 0;
+    Z[C] = n;
+    for (int i = 1; i < C; ++i) Z[i] = F[i] + T * r;
+    std::vector<cudaEvent_t> up(C), done(C);
+    cudaEvent_t ev[4];
+    for (auto& e : ev) CU_TRY(cudaEventCreate(&e));
+    for (int i = 0; i < C; ++i) {
+        CU_TRY(cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
+        CU_TRY(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+    }
+    CU_TRY(cudaEventRecord(ev[0], st));
+    CU_TRY(cudaStreamWaitEvent(S.st_in, ev[0], 0));
+    // upload chunk i = padded outer indices [U_i, U_i+1)
+    for (int i = 0; i < C; ++i) {
+        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
+        CU_TRY(cudaMemcpyAsync((char*)S.staging + ub * outer_bytes, (const char*)in + ub * outer_bytes,
+                               (size_t)(ue - ub) * outer_bytes, cudaMemcpyHostToDevice, S.st_in));
+        CU_TRY(cudaEventRecord(up[i], S.st_in));
+    }
+    CU_TRY(cudaEventRecord(ev[1], S.st_in));
+    // block sizes: the short remainder block FIRST, so block sizes never decrease
+    std::vector<int> blocks;
+    if (T % c.k) blocks.push_back((int)(T % c.k));
+    for (long long b = 0; b < T / c.k; ++b) blocks.push_back(c.k);
+    const Domain dom = make_domain(g, 1, 1);
+    void* buf[2] = {S.buf[0], S.buf[1]};
+    uint32_t nl = 0;
+    // Consecutive parallelograms alternate between two sweep streams and run as a wavefront:
+    // block b of parallelogram i+1 only waits for block b-1 of parallelogram i (its slanted
+    // left halo; the same edge orders the write-after-read on the ping-pong buffer), so the
+    // thin range launches of neighbouring parallelograms fill each other's partial waves.
+    int NS = 2;
+    if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) >= 2 ? 2 : 1;
+    const size_t nb = blocks.size();
+    std::vector<cudaEvent_t> unpacked(C), bd((size_t)C * nb);
+    for (auto& e : unpacked) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : bd) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
+    for (int i = 0; i < C; ++i) {
+        cudaStream_t ss = S.st_sweep[i % NS];
+        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
+        CU_TRY(cudaStreamWaitEvent(ss, up[i], 0));
+        {
+            const long long rb = ub * rows_per_outer, re = ue * rows_per_outer;
+            dim3 grid((unsigned)((g.pitch_x + 255) / 256), (unsigned)((re - rb) < 65535 ? (re - rb) : 65535));
+            if (desc->dtype == SB200_F64)
+                unpack_dense2_kernel<double><<<grid, 256, 0, ss>>>((const double*)S.staging, (double*)buf[0], (double*)buf[1], g, hx, rb, re);
+            else
+                unpack_dense2_kernel<float><<<grid, 256, 0, ss>>>((const float*)S.staging, (float*)buf[0], (float*)buf[1], g, hx, rb, re);
+            CU_TRY(cudaGetLastError());
+        }
+        CU_TRY(cudaEventRecord(unpacked[i], ss));
+        long long done_steps = 0;
+        for (size_t b = 0; b < nb; ++b) {
+            done_steps += blocks[b];
+            long long L = i == 0 ? 0 : Z[i] - done_steps * r;
+            long long R = i == C - 1 ? n : Z[i + 1] - done_steps * r;
+            if (L < 0) L = 0;
+            if (R > n) R = n;
+            if (i > 0) CU_TRY(cudaStreamWaitEvent(ss, b == 0 ? unpacked[i - 1] : bd[(size_t)(i - 1) * nb + b - 1], 0));
+            if (R > L) {
+                if (int rc = pass(desc, c, g, dom, buf[b & 1], buf[(b + 1) & 1], blocks[b], L, R, ss)) return rc;
+                ++nl;
+            }
+            if (i + 1 < C) CU_TRY(cudaEventRecord(bd[(size_t)i * nb + b], ss));
+        }
+        CU_TRY(cudaEventRecord(done[i], ss));
+        CU_TRY(cudaStreamWaitEvent(S.st_out, done[i], 0));
+        if (i == 0) CU_TRY(cudaEventRecord(ev[2], S.st_out));
+        void* host_dst = (desc->iterations & 1u) ? out : in;
+        if (int rc = download_interior_range(desc, buf[nb & 1], host_dst, F[i], F[i + 1], S.st_out)) return rc;
+    }
+    CU_TRY(cudaEventRecord(ev[3], S.st_out));
+    CU_TRY(cudaStreamWaitEvent(st, ev[3], 0));
+    CU_TRY(cudaStreamSynchronize(S.st_out));
+    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamSynchronize(S.st_sweep[q]));
+    CU_TRY(cudaStreamSynchronize(st));
+    CU_TRY(cudaStreamSynchronize(S.st_in));
+    const auto w1 = std::chrono::steady_clock::now();
+    if (timing) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev[0], ev[1]); timing->h2d_ms = ms;    // all upload chunks
+        cudaEventElapsedTime(&ms, ev[0], ev[3]); timing->sweep_ms = ms;  // whole pipeline on the device
+        cudaEventElapsedTime(&ms, ev[2], ev[3]); timing->d2h_ms = ms;    // first to last download chunk
+        timing->wall_ms = std::chrono::duration<double, std::milli>(w1 - w0).count();
+        timing->launches = nl;
+        timing->time_block = (uint32_t)c.k;
+        timing->kernel = c.kernel;
+        timing->result_in_out = (int)(desc->iterations & 1u);
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    for (int i = 0; i < C; ++i) {
+        cudaEventDestroy(up[i]);
+        cudaEventDestroy(done[i]);
+        cudaEventDestroy(unpacked[i]);
+    }
+    for (auto& e : bd) cudaEventDestroy(e);
+    return SB200_OK;
+}
+
 int sb200_upload(const sb200_desc* desc, uint32_t ghost, const void* host, void* dev, void* stream) {
     if (int rc = validate(desc)) return rc;
     if (!host || !dev) return fail(SB200_ERR_INVALID, "null buffer");
@@ -679,6 +883,14 @@ int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* ti
         CU_TRY(cudaMalloc(&S.buf[0], bytes));
         CU_TRY(cudaMalloc(&S.buf[1], bytes));
         S.buf_bytes = bytes;
+    }
+    {
+        const Choice c = choose(desc);
+        if (int rc = check_choice(desc, c)) return rc;
+        const long long hx0 = g.n[0] + 2 * g.r;
+        const size_t dense0 = (size_t)hx0 * g.pitch_y * g.planes * esize(desc->dtype);
+        const int C = pipeline_chunks(desc, c, g, dense0);
+        if (C > 1) return run_host_pipelined(desc, c, in, out, timing, C);
     }
     cudaStream_t st = 0;
     cudaEvent_t ev[4];

@@ -62,6 +62,27 @@ __global__ void unpack_dense_kernel(const T* __restrict__ dense, T* __restrict__
     }
 }
 
+// Same for the rows [row_begin, row_end) only, written into BOTH device grids (the two
+// reference matrices carry the same halo, stencil.cpp:190-207): the unpack step of the
+// pipelined host path, one call per uploaded chunk.
+template <class T>
+__global__ void unpack_dense2_kernel(const T* __restrict__ dense, T* __restrict__ a, T* __restrict__ b,
+                                     Grid g, long long hx, long long row_begin, long long row_end) {
+    const long long x0 = g.ox - g.r;
+    for (long long row = row_begin + blockIdx.y; row < row_end; row += gridDim.y) {
+        const T* src = dense + row * hx;
+        T* da = a + row * g.pitch_x;
+        T* db = b + row * g.pitch_x;
+        for (long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x; px < g.pitch_x;
+             px += (long long)gridDim.x * blockDim.x) {
+            const long long dx = px - x0;
+            const T v = (dx >= 0 && dx < hx) ? src[dx] : T(0);
+            da[px] = v;
+            db[px] = v;
+        }
+    }
+}
+
 template <class T> struct Bits;
 template <> struct Bits<float> {
     static __device__ uint64_t of(float v) { return (uint64_t)__float_as_uint(v); }

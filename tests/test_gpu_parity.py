@@ -220,3 +220,28 @@ def test_slab_link_self_periodic(gpu, n, T, k, shape, dtype):
     assert words[0] == arrivals and words[1] == arrivals
     got = dg.download(cur)[1 + g:1 + g + nz, 1:-1, 1:-1]
     assert np.array_equal(got.view(np.uint8), np.ascontiguousarray(want).view(np.uint8))
+
+
+@pytest.mark.parametrize("chunks", [2, 3, 5])
+@pytest.mark.parametrize("n,r,shape,dtype,T,k,kernel", [
+    ((96, 80, 72), 1, capi.STAR, np.float64, 7, 2, capi.KERNEL_TMA3D),    # remainder block first
+    ((70, 66, 64), 1, capi.BOX, np.float32, 6, 2, capi.KERNEL_TMA3D),
+    ((130, 61, 90), 1, capi.STAR, np.float32, 9, 3, capi.KERNEL_TMA3D),
+    ((300, 400), 1, capi.BOX, np.float32, 21, 4, capi.KERNEL_WARP2D),
+    ((257, 300), 1, capi.STAR, np.float64, 16, 8, capi.KERNEL_WARP2D),
+    ((64, 48, 80), 2, capi.STAR, np.float64, 5, 1, capi.KERNEL_GENERIC),
+    ((200, 150), 3, capi.BOX, np.float32, 4, 1, capi.KERNEL_GENERIC),
+])
+def test_pipelined_host_path(gpu, monkeypatch, chunks, n, r, shape, dtype, T, k, kernel):
+    """sb200_run_host with the grid cut into (z, t) parallelograms (upload, sweep and download
+    overlapped on three streams): forced on small grids here; same bits as the oracle."""
+    monkeypatch.setenv("SB200_PIPELINE_CHUNKS", str(chunks))
+    t = _check(n, r, shape, dtype, T, time_block=k, kernel=kernel)
+    blocks = -(-T // k)
+    wmin = 4 * k * r
+    last = max(T * r, wmin)
+    if n[-1] > last and (n[-1] - last) // wmin + 1 >= 2:
+        assert t.launches > blocks, "the pipelined path was not taken"
+    monkeypatch.setenv("SB200_PIPELINE_CHUNKS", "1")
+    t1 = _check(n, r, shape, dtype, T, time_block=k, kernel=kernel)
+    assert t1.launches == blocks
