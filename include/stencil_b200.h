@@ -155,6 +155,12 @@ int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* gr
 /* Pinned host memory for callers that want full-speed PCIe copies in sb200_run_host. */
 int sb200_host_alloc(void** ptr, size_t bytes);
 int sb200_host_free(void* ptr);
+/* Page-lock caller-owned host memory in place (for callers that keep their own
+ * allocations, like the reference's `make_unique<T[]>` grids,
+ * boundary_matrix.hpp:59): without it the copies of sb200_run_host are staged
+ * by the driver and cannot overlap with the sweep.  Costs ~0.1 ms per MB once. */
+int sb200_host_register(void* ptr, size_t bytes);
+int sb200_host_unregister(void* ptr);
 
 /* ---- multi-GPU slab link: halo exchange fused into the sweep kernel ------------
  * One process per GPU.  Replaces the reference's on-chip RMA halo puts + reply

@@ -26,6 +26,7 @@ SYMBOLS = [
     "sb200_checksum_device", "sb200_host_alloc", "sb200_host_free", "sb200_max_time_block",
     "sb200_device_alloc", "sb200_device_free", "sb200_ipc_export", "sb200_ipc_open",
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
+    "sb200_host_register", "sb200_host_unregister",
 ]
 IPC_HANDLE_BYTES = 64
 LINK_FLAG_WORDS = 4
@@ -102,6 +103,8 @@ def lib() -> ctypes.CDLL:
         L.sb200_checksum_device.argtypes = [dp, u32, vp, u64, u64, vp, ctypes.POINTER(u64)]
         L.sb200_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_host_free.argtypes = [vp]
+        L.sb200_host_register.argtypes = [vp, ctypes.c_size_t]
+        L.sb200_host_unregister.argtypes = [vp]
         L.sb200_max_time_block.argtypes = [dp]
         L.sb200_device_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_device_free.argtypes = [vp]

@@ -865,6 +865,20 @@ int sb200_host_free(void* ptr) {
     return SB200_OK;
 }
 
+int sb200_host_register(void* ptr, size_t bytes) {
+    if (!ptr || bytes == 0) return fail(SB200_ERR_INVALID, "bad host range");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    CU_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    return SB200_OK;
+}
+
+int sb200_host_unregister(void* ptr) {
+    if (!ptr) return SB200_OK;
+    CU_TRY(cudaHostUnregister(ptr));
+    return SB200_OK;
+}
+
 int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* timing) {
     if (int rc = validate(desc)) return rc;
     if (!in || !out) return fail(SB200_ERR_INVALID, "null host buffer");
