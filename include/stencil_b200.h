@@ -209,6 +209,22 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
  * device): words[2] != 0 means a face CTA timed out waiting for a neighbour. */
 int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLAG_WORDS]);
 
+/* What the library WOULD do for `steps` steps of this descriptor on a whole grid of
+ * a device with `sm_count` SMs — pure host logic, no device needed (tests, tuning,
+ * the experiment driver's block-size column).  Meaning of the geometry fields:
+ *   TMA3D:      tiles_x x tiles_y xy tiles, `chunks` z chunks of `chunk_extent` planes
+ *   WARP2D:     tiles_x strips of 128 columns, `chunks` row chunks of `chunk_extent` rows
+ *   RESIDENT2D: tiles_x x tiles_y warp tiles of 128 x chunk_extent points on `chunks` CTAs
+ *   GENERIC:    all zero */
+typedef struct sb200_plan_info {
+    int32_t kernel;           /* sb200_kernel family */
+    uint32_t time_block;      /* fused steps per launch (RESIDENT2D: all of them) */
+    uint32_t launches;        /* kernel launches for `steps` steps */
+    uint32_t tiles_x, tiles_y, chunks, chunk_extent;
+    uint32_t pipeline_chunks; /* (z,t) parallelograms of sb200_run_host; 1 = not pipelined */
+} sb200_plan_info;
+int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_info* info);
+
 /* Largest time block the chosen kernel family supports for this descriptor. */
 int sb200_max_time_block(const sb200_desc* desc);
 

@@ -26,7 +26,7 @@ SYMBOLS = [
     "sb200_checksum_device", "sb200_host_alloc", "sb200_host_free", "sb200_max_time_block",
     "sb200_device_alloc", "sb200_device_free", "sb200_ipc_export", "sb200_ipc_open",
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
-    "sb200_host_register", "sb200_host_unregister",
+    "sb200_host_register", "sb200_host_unregister", "sb200_plan",
 ]
 IPC_HANDLE_BYTES = 64
 LINK_FLAG_WORDS = 4
@@ -63,6 +63,14 @@ class SlabLink(ctypes.Structure):
         ("peer_dst_lo", ctypes.c_void_p), ("peer_dst_hi", ctypes.c_void_p),
         ("flags_local", ctypes.c_void_p), ("flags_lo", ctypes.c_void_p),
         ("flags_hi", ctypes.c_void_p), ("wait_arrivals", ctypes.c_uint32),
+    ]
+
+
+class PlanInfo(ctypes.Structure):
+    _fields_ = [
+        ("kernel", ctypes.c_int32), ("time_block", ctypes.c_uint32), ("launches", ctypes.c_uint32),
+        ("tiles_x", ctypes.c_uint32), ("tiles_y", ctypes.c_uint32), ("chunks", ctypes.c_uint32),
+        ("chunk_extent", ctypes.c_uint32), ("pipeline_chunks", ctypes.c_uint32),
     ]
 
 
@@ -105,6 +113,7 @@ def lib() -> ctypes.CDLL:
         L.sb200_host_free.argtypes = [vp]
         L.sb200_host_register.argtypes = [vp, ctypes.c_size_t]
         L.sb200_host_unregister.argtypes = [vp]
+        L.sb200_plan.argtypes = [dp, u32, i32, ctypes.POINTER(PlanInfo)]
         L.sb200_max_time_block.argtypes = [dp]
         L.sb200_device_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_device_free.argtypes = [vp]
@@ -141,3 +150,10 @@ def layout_for(desc: Desc, ghost: int = 0) -> Layout:
     lay = Layout()
     check(lib().sb200_layout_for(ctypes.byref(desc), ghost, ctypes.byref(lay)))
     return lay
+
+
+def plan(desc: Desc, steps: int, sm_count: int = 148) -> PlanInfo:
+    """Kernel family / fused depth / geometry the library would use (host logic only)."""
+    info = PlanInfo()
+    check(lib().sb200_plan(ctypes.byref(desc), steps, sm_count, ctypes.byref(info)))
+    return info

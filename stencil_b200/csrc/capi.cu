@@ -410,6 +410,65 @@ int sb200_layout_for(const sb200_desc* desc, uint32_t ghost, sb200_layout* layou
     return SB200_OK;
 }
 
+static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, size_t dense_bytes);
+
+int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_info* info) {
+    if (int rc = validate(desc)) return rc;
+    if (!info || sm_count < 1) return fail(SB200_ERR_INVALID, "bad argument");
+    memset(info, 0, sizeof *info);
+    Choice c = choose(desc);
+    if (int rc = check_choice(desc, c)) return rc;
+    const Grid g = make_grid(desc, 0);
+    const int es = (int)esize(desc->dtype);
+    bool resident = c.kernel == SB200_KERNEL_RESIDENT2D;
+    if (desc->kernel == SB200_KERNEL_AUTO && desc->time_block == 0 && c.kernel == SB200_KERNEL_WARP2D &&
+        steps >= 16 && resident2d_fits(g.n[0], g.n[1], es))
+        resident = true;
+    info->pipeline_chunks = 1;
+    if (resident) {
+        int ncta, cx, wr, R;
+        resident2d_layout(g.n[0], g.n[1], es, &ncta, &cx, &wr, &R);
+        info->kernel = SB200_KERNEL_RESIDENT2D;
+        info->time_block = steps;
+        info->launches = steps > 0 ? 1 : 0;
+        info->tiles_x = (uint32_t)cx;
+        info->tiles_y = (uint32_t)wr;
+        info->chunks = (uint32_t)ncta;
+        info->chunk_extent = (uint32_t)R;
+        return SB200_OK;
+    }
+    info->kernel = c.kernel;
+    info->time_block = (uint32_t)c.k;
+    info->launches = (steps + c.k - 1) / c.k;
+    const int k = steps && steps < (uint32_t)c.k ? (int)steps : c.k;
+    if (c.kernel == SB200_KERNEL_WARP2D) {
+        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count);
+        info->tiles_x = (uint32_t)p.nstrips;
+        info->tiles_y = 1;
+        info->chunks = (uint32_t)p.nchunks;
+        info->chunk_extent = (uint32_t)p.chunk_rows;
+    } else if (c.kernel == SB200_KERNEL_TMA3D) {
+        T3Plan p;
+        if (desc->dtype == SB200_F64)
+            p = k == 1 ? t3_plan<double, 1>(g.n[0], g.n[1], g.n[2], sm_count)
+                : k == 2 ? t3_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count)
+                         : t3_plan<double, 3>(g.n[0], g.n[1], g.n[2], sm_count);
+        else
+            p = k == 1 ? t3_plan<float, 1>(g.n[0], g.n[1], g.n[2], sm_count)
+                : k == 2 ? t3_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count)
+                         : t3_plan<float, 3>(g.n[0], g.n[1], g.n[2], sm_count);
+        info->tiles_x = (uint32_t)p.ntx;
+        info->tiles_y = (uint32_t)p.nty;
+        info->chunks = (uint32_t)p.nchunks;
+        info->chunk_extent = (uint32_t)p.chunk_planes;
+    }
+    sb200_desc d2 = *desc;
+    d2.iterations = steps;
+    const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * (size_t)es;
+    info->pipeline_chunks = (uint32_t)pipeline_chunks(&d2, c, g, dense);
+    return SB200_OK;
+}
+
 int sb200_max_time_block(const sb200_desc* desc) {
     if (int rc = validate(desc)) return rc;
     const Choice c = choose(desc);

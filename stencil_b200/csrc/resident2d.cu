@@ -66,6 +66,14 @@ int resident2d_fits(long long nx, long long ny, int elem_size) {
     return rs_plan(nx, ny, elem_size).ok ? 1 : 0;
 }
 
+void resident2d_layout(long long nx, long long ny, int elem_size, int* ncta, int* cx, int* wr, int* R) {
+    const RsPlan p = rs_plan(nx, ny, elem_size);
+    *ncta = p.ok ? p.ncta : 0;
+    *cx = p.ok ? p.cx : 0;
+    *wr = p.ok ? p.wr : 0;
+    *R = p.ok ? p.R : 0;
+}
+
 cudaError_t launch_resident2d(const void* in, void* out, const Grid& g, int shape, int elem_size, int steps,
                               cudaStream_t st) {
     const RsPlan p = rs_plan(g.n[0], g.n[1], elem_size);

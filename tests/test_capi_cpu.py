@@ -69,3 +69,35 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "liboracle" not in src, f
+
+
+def test_plan_host_logic(monkeypatch):
+    """sb200_plan: kernel choice, fused depth, tiling and pipelining decisions need no GPU."""
+    monkeypatch.delenv("SB200_PIPELINE_CHUNKS", raising=False)
+    # config 2: 512^3 fp64 7-point, T=100 -> TMA3D k=2, 9x9 tiles of 60x60, 9 z chunks, 8 parallelograms
+    p = capi.plan(capi.make_desc((512, 512, 512), 1, capi.STAR, capi.F64, 100), 100)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_TMA3D, 2, 50)
+    assert (p.tiles_x, p.tiles_y) == (9, 9) and p.chunks * p.chunk_extent >= 512
+    assert p.chunks * p.tiles_x * p.tiles_y >= 148 and p.pipeline_chunks == 8
+    # config 4: 16384^2 fp32 9-point, T=1000 -> WARP2D k=4, one strip per ~120 columns
+    p = capi.plan(capi.make_desc((16384, 16384), 1, capi.BOX, capi.F32, 1000), 1000)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 4, 250)
+    assert p.tiles_x == -(-16384 // 120) and p.chunks * p.chunk_extent >= 16384 and p.pipeline_chunks == 8
+    # the reference's own run.sh grid: resident in one cluster, one launch, not pipelined
+    p = capi.plan(capi.make_desc((400, 400), 1, capi.STAR, capi.F32, 1000), 1000)
+    assert (p.kernel, p.launches, p.pipeline_chunks) == (capi.KERNEL_RESIDENT2D, 1, 1)
+    assert p.tiles_x == 4 and p.tiles_x * p.tiles_y <= 16 * p.chunks and p.tiles_y * p.chunk_extent >= 400
+    # too few steps for the resident kernel, too large for it, radius 2, 1-D
+    assert capi.plan(capi.make_desc((400, 400), 1, capi.STAR, capi.F32, 8), 8).kernel == capi.KERNEL_WARP2D
+    p = capi.plan(capi.make_desc((960, 960), 1, capi.STAR, capi.F32, 1000), 1000)
+    assert p.kernel == capi.KERNEL_WARP2D and p.chunk_extent < 64  # small-grid planner: short chunks
+    assert capi.plan(capi.make_desc((400, 400), 2, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    p = capi.plan(capi.make_desc((1 << 20,), 1, capi.STAR, capi.F64, 10), 10)
+    assert (p.kernel, p.launches, p.pipeline_chunks) == (capi.KERNEL_GENERIC, 10, 1)
+    # T*r too long for the grid: the last parallelogram cannot start inside it -> not pipelined
+    p = capi.plan(capi.make_desc((512, 512, 512), 1, capi.STAR, capi.F64, 600), 600)
+    assert p.pipeline_chunks == 1
+    monkeypatch.setenv("SB200_PIPELINE_CHUNKS", "3")
+    assert capi.plan(capi.make_desc((96, 80, 72), 1, capi.STAR, capi.F64, 7), 7).pipeline_chunks == 3
+    with pytest.raises(capi.StencilError):
+        capi.plan(capi.make_desc((2000, 2000), 1, capi.STAR, capi.F32, 10, kernel=capi.KERNEL_RESIDENT2D), 10)
