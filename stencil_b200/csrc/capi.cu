@@ -73,7 +73,7 @@ struct State {
     // pipelined host path: dense staging image + copy-in / copy-out streams
     void* staging = nullptr;
     size_t staging_bytes = 0;
-    cudaStream_t st_in = nullptr, st_out = nullptr, st_sweep[2] = {nullptr, nullptr};
+    cudaStream_t st_in = nullptr, st_out = nullptr, st_sweep[4] = {nullptr, nullptr, nullptr, nullptr};
 } S;
 std::mutex g_mu;
 
@@ -800,7 +800,7 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     // left halo; the same edge orders the write-after-read on the ping-pong buffer), so the
     // thin range launches of neighbouring parallelograms fill each other's partial waves.
     int NS = 2;
-    if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) >= 2 ? 2 : 1;
+    if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) < 1 ? 1 : (atoi(e) > 4 ? 4 : atoi(e));
     const size_t nb = blocks.size();
     std::vector<cudaEvent_t> unpacked(C), bd((size_t)C * nb);
     for (auto& e : unpacked) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));

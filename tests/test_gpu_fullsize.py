@@ -80,3 +80,22 @@ def test_linearity_of_the_sweep(gpu):
     r1 = g1.bufs()[0].view(torch.float64)
     r2 = g2.bufs()[0].view(torch.float64)
     assert torch.equal(r1 * 2.0, r2)
+
+
+@pytest.mark.parametrize("name,n,shape,dtype,T", [
+    ("config2", (512, 512, 512), capi.STAR, np.float64, 100),
+    ("config1-f64", (4096, 4096), capi.STAR, np.float64, 100),
+    ("config3", (512, 512, 512), capi.BOX, np.float64, 51),
+])
+def test_full_size_drop_in_call_matches_oracle(gpu, name, n, shape, dtype, T):
+    """The drop-in call itself (sb200_run_host: pipelined upload / sweep / download in (z,t)
+    parallelograms at these sizes) against the oracle, every point, halo untouched."""
+    code = oracle.F64 if dtype == np.float64 else oracle.F32
+    a = oracle.fill(n, 1, code, oracle.INIT_RANDOM, 3)
+    b = oracle.fill(n, 1, code, oracle.INIT_REF)
+    ga, gb = a.copy(), b.copy()
+    want = b if oracle.sweep(n, 1, shape, T, a, b, threads=oracle.max_threads()) else a
+    got, t = sweep.run_host(n, ga, gb, T, shape=shape)
+    assert t.launches > -(-T // t.time_block), "expected the pipelined path at this size"
+    assert got is (gb if T & 1 else ga)
+    assert np.array_equal(want.view(np.uint8), got.view(np.uint8)), name
