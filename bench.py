@@ -104,6 +104,15 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_threads() -> int:
+    """Host cores this process may use.  Not omp_get_max_threads(): torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which would silently time a 1-thread baseline."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_sample(threads: int, budget_s: float = 12.0):
     """Time the oracle port on the workload grid for a bounded number of steps."""
     import oracle
@@ -129,7 +138,7 @@ def run_reference(args):
         return
     import oracle
     oracle.lib()
-    threads = oracle.max_threads()
+    threads = host_threads()
     n = (N_SIDE, N_SIDE, N_SIDE)
     a = oracle.fill(n, 1, oracle.F64, oracle.INIT_RANDOM, seed=1)
     b = oracle.fill(n, 1, oracle.F64, oracle.INIT_REF)
@@ -260,8 +269,7 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        import oracle
-        threads = oracle.max_threads()
+        threads = host_threads()
         v, s, dt = cpu_sample(threads)
         cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{s} time steps of the full 512^3 fp64 grid ({dt:.1f} s; the workload runs {T_STEPS}), "
