@@ -37,7 +37,7 @@ struct ProgramOptions {
     unsigned time_block = 0;      // fused steps per HBM round trip; 0 = auto
     std::string init = "ref";     // ref | random
     unsigned long long seed = 1;
-    std::string kernel = "auto";  // auto | generic | warp2d | tma3d
+    std::string kernel = "auto";  // auto | generic | warp2d | tma3d | resident2d
     std::string json_path;        // append one JSON record per method here
     std::string bmp_path;         // write the final 2-D field as a BMP heat map
 

@@ -107,6 +107,7 @@ sb200_desc make_desc(ProgramOptions const& o) {
     d.kernel = o.kernel == "generic" ? SB200_KERNEL_GENERIC
                : o.kernel == "warp2d" ? SB200_KERNEL_WARP2D
                : o.kernel == "tma3d"  ? SB200_KERNEL_TMA3D
+               : o.kernel == "resident2d" ? SB200_KERNEL_RESIDENT2D
                                       : SB200_KERNEL_AUTO;
     return d;
 }
