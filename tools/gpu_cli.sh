@@ -10,6 +10,6 @@ L=gpurun_out/cli.log
   $BIN -s 4096 -i 100 -b 64 -r 1 -R 3 -m CUDA -c;
   echo; echo "\$ ./run.sh -R 3 -c"; bash run.sh -R 3 -c;
   echo; echo "\$ stencil_main --shape 512,512,512 --dtype f64 -i 100 -b 64 -R 3 -m CUDA";
-  $BIN --shape 512,512,512 --dtype f64 -i 100 -b 64 -R 3 -m CUDA; } > $L 2>&1
+  $BIN -s 512 --shape 512,512,512 --dtype f64 -i 100 -b 64 -R 3 -m CUDA; } > $L 2>&1
 tail -40 $L
 python run_expr.py --iters 1000 100000 --repeat 2 --out gpurun_out/run_expr.csv > gpurun_out/run_expr.log 2>&1; cat gpurun_out/run_expr.csv
