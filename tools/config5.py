@@ -64,11 +64,18 @@ if world > 1:
     dist.all_reduce(cs)
 total = (int(cs[0]) + (int(cs[1]) << 31) + (int(cs[2]) << 62)) % (1 << 64)
 pts = args.nxy * args.nxy * nz_local * world
+# halo traffic of an interior rank: 2 faces x ghost planes out (and as many in) per fused block
+blocks = -(-args.steps // sw.time_block)
+face_bytes = 2 * sw.ghost * args.nxy * args.nxy * 8 if world > 1 else 0
+nvlink_gbs = face_bytes * blocks / (best * 1e-3) / 1e9
 if rank == 0:
     gs = pts * args.steps / best / 1e6
     print(json.dumps({"config": 5, "mode": args.mode, "n_gpus": world, "grid_zyx": [nz_local * world, args.nxy, args.nxy],
                       "steps": args.steps, "time_block": sw.time_block, "exchange": sw.exchange, "ms": best, "GStencil/s": gs,
-                      "alg_GBps_per_gpu": gs * 16 / world, "checksum": f"{total:#018x}"}), flush=True)
+                      "alg_GBps_per_gpu": gs * 16 / world,
+                      "hbm_roofline_frac_per_gpu": gs * 16 / world / 6545.3,
+                      "halo_bytes_out_per_block_per_gpu": face_bytes, "nvlink_out_GBps_per_gpu": nvlink_gbs,
+                      "nvlink_frac_of_900GBps": nvlink_gbs / 900.0, "checksum": f"{total:#018x}"}), flush=True)
 sw.close()
 if world > 1:
     dist.destroy_process_group()
