@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SB200_ABI_VERSION 1
+#define SB200_ABI_VERSION 2 /* 2: slab link, resident2d, plan, host_register */
 
 typedef enum sb200_status {
     SB200_OK = 0,
