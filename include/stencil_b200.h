@@ -66,7 +66,13 @@ typedef struct sb200_desc {
     int32_t kernel;      /* sb200_kernel */
 } sb200_desc;
 
-/* Timing breakdown of one call (milliseconds; device times from CUDA events). */
+/* Timing breakdown of one call (milliseconds; device times from CUDA events).
+ * Small grids run upload -> sweep -> download back to back and the three device
+ * times add up.  Grids of >= 64 MB are pipelined (upload, sweep and download of
+ * different (z,t) parallelograms overlap on separate streams); then h2d_ms is the
+ * span of all upload chunks, d2h_ms the span from the first to the last download
+ * chunk, and sweep_ms the span of the WHOLE device pipeline (copies included),
+ * i.e. the three overlap and sweep_ms is the number to divide the updates by. */
 typedef struct sb200_timing {
     double h2d_ms;
     double sweep_ms;
