@@ -42,7 +42,7 @@ typedef enum sb200_init_kind { SB200_INIT_REF = 0, SB200_INIT_RANDOM = 1 } sb200
 typedef enum sb200_kernel {
     SB200_KERNEL_AUTO = 0,
     SB200_KERNEL_GENERIC = 1, /* one step per launch, any ndim/shape/radius   */
-    SB200_KERNEL_WARP2D = 2,  /* 2-D r=1, register/shuffle temporal blocking   */
+    SB200_KERNEL_WARP2D = 2,  /* 2-D r=1 (star/box) and r=2..4 (star): register/shuffle temporal blocking */
     SB200_KERNEL_TMA3D = 3,   /* 3-D r=1, TMA-staged z-streaming, temporal blk */
     SB200_KERNEL_RESIDENT2D = 4 /* small 2-D r=1 grids: register-resident in one
                                    thread-block cluster for ALL steps of a call, one

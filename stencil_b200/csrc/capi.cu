@@ -21,6 +21,7 @@
 #include "tma3d.cuh"
 #include "util_kernels.cuh"
 #include "warp2d.cuh"
+#include "warp2dr.cuh"
 
 using namespace sb200;
 
@@ -228,28 +229,33 @@ struct Choice {
     int k;
 };
 
+// WARP2D family: radius 1 star/box (warp2d.cuh), radius 2..4 star (warp2dr.cuh).
+bool warp2d_supports(const sb200_desc* d) {
+    return d->ndim == 2 && (d->radius == 1 || (d->shape == SB200_STAR && d->radius >= 2 && d->radius <= 4));
+}
+
 Choice choose(const sb200_desc* d) {
     Choice c;
-    const bool w2d_ok = d->ndim == 2 && d->radius == 1;
+    const bool w2d_ok = warp2d_supports(d);
     const bool t3_ok = d->ndim == 3 && d->radius == 1;
     int kern = d->kernel;
     if (kern == SB200_KERNEL_AUTO)
         kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : SB200_KERNEL_GENERIC;
     c.kernel = kern;
-    c.max_k = kern == SB200_KERNEL_WARP2D ? W2D_MAXK
+    c.max_k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? w2r_max_k((int)d->radius, (int)esize(d->dtype)) : W2D_MAXK)
               : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
               : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30) : 1;
     int k = (int)d->time_block;
     if (kern == SB200_KERNEL_RESIDENT2D) k = c.max_k;  // the whole call is one launch
-    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? 4 : kern == SB200_KERNEL_TMA3D ? 2 : 1;
+    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? c.max_k : 4) : kern == SB200_KERNEL_TMA3D ? 2 : 1;
     if (k > c.max_k) k = c.max_k;
     c.k = k;
     return c;
 }
 
 int check_choice(const sb200_desc* d, const Choice& c) {
-    if (c.kernel == SB200_KERNEL_WARP2D && !(d->ndim == 2 && d->radius == 1))
-        return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2, radius=1");
+    if (c.kernel == SB200_KERNEL_WARP2D && !warp2d_supports(d))
+        return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2 and radius=1 (star or box) or radius 2..4 (star)");
     if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
         return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1");
     if (c.kernel == SB200_KERNEL_RESIDENT2D &&
@@ -269,7 +275,10 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             CU_TRY(launch_generic<T>(a, b, g, d->shape, ob, oe, st));
             return SB200_OK;
         case SB200_KERNEL_WARP2D:
-            CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, S.sm_count, st));
+            if (g.r > 1)
+                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, S.sm_count, st));
+            else
+                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, S.sm_count, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
@@ -307,7 +316,7 @@ int sweep_impl(const sb200_desc* d, uint32_t ghost, int lo_b, int hi_b, void* a,
     bool resident = c.kernel == SB200_KERNEL_RESIDENT2D;
     if (resident && !whole) return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel cannot sweep a slab with ghost planes");
     if (d->kernel == SB200_KERNEL_AUTO && d->time_block == 0 && c.kernel == SB200_KERNEL_WARP2D && whole &&
-        steps >= 16 && resident2d_fits(g.n[0], g.n[1], (int)esize(d->dtype)))
+        d->radius == 1 && steps >= 16 && resident2d_fits(g.n[0], g.n[1], (int)esize(d->dtype)))
         resident = true;
     if (resident) {
         if (steps > 0) CU_TRY(launch_resident2d(a, b, g, d->shape, (int)esize(d->dtype), (int)steps, st));
@@ -422,7 +431,7 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     const int es = (int)esize(desc->dtype);
     bool resident = c.kernel == SB200_KERNEL_RESIDENT2D;
     if (desc->kernel == SB200_KERNEL_AUTO && desc->time_block == 0 && c.kernel == SB200_KERNEL_WARP2D &&
-        steps >= 16 && resident2d_fits(g.n[0], g.n[1], es))
+        desc->radius == 1 && steps >= 16 && resident2d_fits(g.n[0], g.n[1], es))
         resident = true;
     info->pipeline_chunks = 1;
     if (resident) {
@@ -442,7 +451,7 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     info->launches = (steps + c.k - 1) / c.k;
     const int k = steps && steps < (uint32_t)c.k ? (int)steps : c.k;
     if (c.kernel == SB200_KERNEL_WARP2D) {
-        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count);
+        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r);
         info->tiles_x = (uint32_t)p.nstrips;
         info->tiles_y = 1;
         info->chunks = (uint32_t)p.nchunks;

@@ -261,14 +261,15 @@ struct W2dPlan {
 // grids — the reference's own N <= 960 regime (run_expr.py:6-14) — cannot fill the machine
 // that way and a launch costs the latency of ONE warp walking its chunk row by row, so they
 // are cut into short chunks (>= 4 rows) until every SM sub-partition has a few warps.
-static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count) {
+// R > 1: the radius-R kernel of warp2dr.cuh, whose halo is K*R per side.
+static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count, int R = 1) {
     W2dPlan p;
-    const int V = (W2D_WIDTH - ((K + 3) & ~3) - K) & ~3;
+    const int V = (W2D_WIDTH - ((K * R + 3) & ~3) - K * R) & ~3;
     p.nstrips = (int)((nx + V - 1) / V);
     const long long want_items = (long long)sm_count * 16 * 2;
     long long nchunks = (want_items + p.nstrips - 1) / p.nstrips;
     long long chunk_rows = (rows + nchunks - 1) / nchunks;
-    const long long min_rows = 16LL * K;
+    const long long min_rows = 16LL * K * R;
     const bool small = ((rows + min_rows - 1) / min_rows) * p.nstrips < (long long)sm_count * 8;
     if (chunk_rows < min_rows && !small) chunk_rows = min_rows;
     if (chunk_rows < min_rows && small) {

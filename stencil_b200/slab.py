@@ -32,15 +32,19 @@ _KERNEL_NAMES = {capi.KERNEL_GENERIC: "generic", capi.KERNEL_WARP2D: "warp2d",
 def resolve_kernel(desc: capi.Desc):
     """(family, fused depth) the library will use for this descriptor (mirrors choose()
     in csrc/capi.cu; max depth is asked from the library)."""
-    w2d = desc.ndim == 2 and desc.radius == 1
+    star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
+    w2d = desc.ndim == 2 and (desc.radius == 1 or star_r)
     t3 = desc.ndim == 3 and desc.radius == 1
-    box = desc.shape == capi.BOX
     kern = desc.kernel
     if kern == capi.KERNEL_AUTO:
         kern = capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3 else capi.KERNEL_GENERIC
-    max_k = {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 8, capi.KERNEL_TMA3D: 2 if box else 3}[kern]
-    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_WARP2D: 4,
-                            capi.KERNEL_TMA3D: 2}[kern]
+    d = capi.Desc.from_buffer_copy(desc)
+    d.kernel = kern
+    max_k = int(capi.lib().sb200_max_time_block(ctypes.byref(d)))
+    if max_k < 1:
+        raise capi.StencilError(max_k, capi.lib().sb200_last_error().decode())
+    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_TMA3D: 2,
+                            capi.KERNEL_WARP2D: 4 if desc.radius == 1 else max_k}[kern]
     return kern, min(k, max_k)
 
 

@@ -93,7 +93,12 @@ def test_plan_host_logic(monkeypatch):
     assert capi.plan(capi.make_desc((400, 400), 1, capi.STAR, capi.F32, 8), 8).kernel == capi.KERNEL_WARP2D
     p = capi.plan(capi.make_desc((960, 960), 1, capi.STAR, capi.F32, 1000), 1000)
     assert p.kernel == capi.KERNEL_WARP2D and p.chunk_extent < 64  # small-grid planner: short chunks
-    assert capi.plan(capi.make_desc((400, 400), 2, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    p = capi.plan(capi.make_desc((400, 400), 2, capi.STAR, capi.F32, 100), 100)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 4, 25)  # radius-2 star: fused warp kernel
+    p = capi.plan(capi.make_desc((400, 400), 4, capi.STAR, capi.F64, 100), 100)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 1, 100)
+    assert capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    assert capi.plan(capi.make_desc((400, 400), 5, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     p = capi.plan(capi.make_desc((1 << 20,), 1, capi.STAR, capi.F64, 10), 10)
     assert (p.kernel, p.launches, p.pipeline_chunks) == (capi.KERNEL_GENERIC, 10, 1)
     # T*r too long for the grid: the last parallelogram cannot start inside it -> not pipelined

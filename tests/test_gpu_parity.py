@@ -72,6 +72,29 @@ def test_warp2d_kernel(gpu, n, T, k, shape, dtype):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,r,T,k", [
+    ((1, 1), 2, 3, 2), ((3, 2), 3, 5, 2), ((120, 50), 2, 4, 4), ((121, 97), 2, 9, 3), ((250, 31), 3, 7, 2),
+    ((500, 300), 4, 6, 2), ((1000, 129), 2, 11, 4), ((777, 555), 3, 5, 1), ((2100, 64), 4, 3, 1),
+    ((119, 200), 2, 7, 2), ((241, 40), 3, 2, 2), ((64, 2000), 4, 5, 2), ((113, 113), 2, 8, 1),
+])
+def test_warp2d_radius_kernel(gpu, n, r, T, k, dtype):
+    """General-radius star (reference -r 2..4) through the fused warp kernel, bit-exact."""
+    kmax = int(capi.lib().sb200_max_time_block(ctypes.byref(
+        capi.make_desc(n, r, capi.STAR, capi.F64 if dtype == np.float64 else capi.F32, T,
+                       kernel=capi.KERNEL_WARP2D))))
+    assert kmax == {(2, 4): 4, (3, 4): 2, (4, 4): 2, (2, 8): 2, (3, 8): 2, (4, 8): 1}[(r, np.dtype(dtype).itemsize)]
+    t = _check(n, r, capi.STAR, dtype, T, time_block=k, kernel=capi.KERNEL_WARP2D)
+    ke = min(k, kmax)
+    assert t.kernel == capi.KERNEL_WARP2D and t.time_block == ke and t.launches == -(-T // ke)
+
+
+def test_warp2d_radius_box_is_unsupported(gpu):
+    d = capi.make_desc((64, 64), radius=2, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
+    a = np.zeros((68, 68), np.float32)
+    assert capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, a.ctypes.data, None) == capi.ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("n,T,k", [
     ((1, 1, 1), 3, 2), ((5, 4, 3), 4, 3), ((60, 60, 20), 4, 2), ((61, 59, 33), 5, 2),
     ((130, 70, 40), 6, 3), ((200, 130, 17), 3, 1), ((123, 125, 64), 7, 3), ((300, 64, 9), 2, 2),
@@ -96,7 +119,9 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70, 60), 1, capi.STAR, np.float64, 4).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
-    assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
+    assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70), 5, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
 
 
 def test_ref_init_denormals_preserved(gpu):

@@ -14,8 +14,8 @@ capi.check(capi.lib().sb200_init(0))
 PEAK = 6529.1
 
 
-def run(name, n, shape, dtype, T, kernel, k, reps=3):
-    d = capi.make_desc(n, 1, shape, dtype, T, time_block=k, kernel=kernel)
+def run(name, n, shape, dtype, T, kernel, k, reps=3, r=1):
+    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel)
     try:
         g = sweep.DeviceGrids(d)
         g.fill(capi.INIT_RANDOM, seed=1)
@@ -64,3 +64,11 @@ if "c3" in which:
     for k in (1, 2):
         run("c3-27pt", (512, 512, 512), capi.BOX, capi.F64, 12, capi.KERNEL_TMA3D, k)
         run("c3-27pt-f32", (512, 512, 512), capi.BOX, capi.F32, 12, capi.KERNEL_TMA3D, k)
+if "rad" in which:  # general-radius 2-D star: fused warp kernel vs the one-thread-per-point kernel
+    for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
+        for r in (2, 3, 4):
+            for k in (1, 2, 3, 4):
+                if k <= capi.lib().sb200_max_time_block(ctypes.byref(
+                        capi.make_desc((8192, 8192), r, capi.STAR, dt, 24, kernel=capi.KERNEL_WARP2D))):
+                    run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 24, capi.KERNEL_WARP2D, k, r=r)
+            run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 8, capi.KERNEL_GENERIC, 1, r=r)
