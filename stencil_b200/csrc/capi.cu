@@ -720,11 +720,11 @@ static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, 
     const long long n = outer_n(g);
     const long long reach = (long long)d->iterations * d->radius;  // planes a parallelogram drifts
     const long long wmin = 4LL * c.k * d->radius;                  // narrowest final region
-    // the LAST final region must be at least `reach` wide (its parallelogram starts at the
-    // high end of the grid); the others only need to be wider than their halos
+    // starting edges are n/(C-1) apart and must be wider than their halos; nothing can be
+    // downloaded early unless the grid is longer than the drift
     const long long last = reach > wmin ? reach : wmin;
-    long long cmax = n > last ? (n - last) / wmin + 1 : 1;
-    long long want = 8;
+    long long cmax = n > last ? n / wmin + 1 : 1;
+    long long want = 11;
     if (const char* e = getenv("SB200_PIPELINE_CHUNKS")) want = atoll(e);
     else if (dense_bytes < (64u << 20)) want = 1;  // small grids: the copies are too short to hide
     if (want > cmax) want = cmax;
@@ -766,20 +766,17 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         for (auto& q : S.st_sweep) CU_TRY(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
     }
     cudaStream_t st = 0;  // the caller's stream: start / end of the whole pipeline
-    // final regions F_i (equal download chunks) and starting edges Z_i = F_i + T*r
+    // Starting edges Z_i: C-1 equal upload chunks, then a last parallelogram that starts with
+    // zero width at the high end (a triangle growing to T*r planes).  Final regions
+    // F_i = Z_i - T*r clipped at 0: parallelograms that drift out of the grid before step T
+    // (the first ~T*r planes) download nothing, so the first upload chunk does not have to
+    // cover the whole drift before sweeping starts.
     std::vector<long long> F(C + 1), Z(C + 1);
-    // final regions: the last one is `reach` (>= 4k*r) wide, the others split the rest evenly
-    {
-        const long long wmin = 4LL * c.k * r;
-        long long last = T * r > wmin ? T * r : wmin;
-        if (const char* e = getenv("SB200_PIPELINE_LAST")) last = atoll(e) > last ? atoll(e) : last;
-        F[0] = 0;
-        for (int i = 1; i < C; ++i) F[i] = (n - last) * i / (C - 1);
-        F[C] = n;
+    for (int i = 0; i < C; ++i) {
+        Z[i] = n * i / (C - 1);
+        F[i] = Z[i] - T * r > 0 ? Z[i] - T * r : 0;
     }
-    Z[0] = 0;
-    Z[C] = n;
-    for (int i = 1; i < C; ++i) Z[i] = F[i] + T * r;
+    Z[C] = F[C] = n;
     std::vector<cudaEvent_t> up(C), done(C);
     cudaEvent_t ev[4];
     for (auto& e : ev) CU_TRY(cudaEventCreate(&e));
@@ -815,6 +812,7 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     for (auto& e : unpacked) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto& e : bd) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
+    bool first_download = false;
     for (int i = 0; i < C; ++i) {
         cudaStream_t ss = S.st_sweep[i % NS];
         const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
@@ -845,7 +843,10 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         }
         CU_TRY(cudaEventRecord(done[i], ss));
         CU_TRY(cudaStreamWaitEvent(S.st_out, done[i], 0));
-        if (i == 0) CU_TRY(cudaEventRecord(ev[2], S.st_out));
+        if (!first_download && (F[i + 1] > F[i] || i == C - 1)) {
+            CU_TRY(cudaEventRecord(ev[2], S.st_out));
+            first_download = true;
+        }
         void* host_dst = (desc->iterations & 1u) ? out : in;
         if (int rc = download_interior_range(desc, buf[nb & 1], host_dst, F[i], F[i + 1], S.st_out)) return rc;
     }

@@ -76,15 +76,15 @@ def test_product_never_imports_oracle():
 def test_plan_host_logic(monkeypatch):
     """sb200_plan: kernel choice, fused depth, tiling and pipelining decisions need no GPU."""
     monkeypatch.delenv("SB200_PIPELINE_CHUNKS", raising=False)
-    # config 2: 512^3 fp64 7-point, T=100 -> TMA3D k=2, 9x9 tiles of 60x60, 9 z chunks, 8 parallelograms
+    # config 2: 512^3 fp64 7-point, T=100 -> TMA3D k=2, 9x9 tiles of 60x60, 9 z chunks, 11 parallelograms
     p = capi.plan(capi.make_desc((512, 512, 512), 1, capi.STAR, capi.F64, 100), 100)
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_TMA3D, 2, 50)
     assert (p.tiles_x, p.tiles_y) == (9, 9) and p.chunks * p.chunk_extent >= 512
-    assert p.chunks * p.tiles_x * p.tiles_y >= 148 and p.pipeline_chunks == 8
+    assert p.chunks * p.tiles_x * p.tiles_y >= 148 and p.pipeline_chunks == 11
     # config 4: 16384^2 fp32 9-point, T=1000 -> WARP2D k=4, one strip per ~120 columns
     p = capi.plan(capi.make_desc((16384, 16384), 1, capi.BOX, capi.F32, 1000), 1000)
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 4, 250)
-    assert p.tiles_x == -(-16384 // 120) and p.chunks * p.chunk_extent >= 16384 and p.pipeline_chunks == 8
+    assert p.tiles_x == -(-16384 // 120) and p.chunks * p.chunk_extent >= 16384 and p.pipeline_chunks == 11
     # the reference's own run.sh grid: resident in one cluster, one launch, not pipelined
     p = capi.plan(capi.make_desc((400, 400), 1, capi.STAR, capi.F32, 1000), 1000)
     assert (p.kernel, p.launches, p.pipeline_chunks) == (capi.KERNEL_RESIDENT2D, 1, 1)

@@ -28,6 +28,6 @@ for rep in range(4):
     capi.check(capi.lib().sb200_run_host(ctypes.byref(desc), hp[0], hp[1], ctypes.byref(tm)))
     dt = time.perf_counter() - t0
     if rep:
-        print(f"chunks={os.environ.get('SB200_PIPELINE_CHUNKS', 'auto')} f1={os.environ.get('SB200_PIPELINE_F1', 'auto')}: "
+        print(f"chunks={os.environ.get('SB200_PIPELINE_CHUNKS', 'auto')}: "
               f"wall {dt * 1e3:7.2f} ms  {N ** 3 * T / dt / 1e9:7.1f} GStencil/s  h2d {tm.h2d_ms:.1f} pipeline {tm.sweep_ms:.1f} "
               f"d2h-span {tm.d2h_ms:.1f} launches {tm.launches}", flush=True)
