@@ -45,6 +45,25 @@ int fail(int code, const char* fmt, ...) {
                         __FILE__, __LINE__);                                               \
     } while (0)
 
+// Owns the CUDA events of one call: destroyed on every return path, errors included.
+struct Events {
+    std::vector<cudaEvent_t> all;
+    cudaError_t err = cudaSuccess;
+    cudaEvent_t make(unsigned flags = cudaEventDisableTiming) {
+        cudaEvent_t e = nullptr;
+        const cudaError_t rc = cudaEventCreateWithFlags(&e, flags);
+        if (rc != cudaSuccess) {
+            if (err == cudaSuccess) err = rc;
+            return nullptr;
+        }
+        all.push_back(e);
+        return e;
+    }
+    ~Events() {
+        for (cudaEvent_t e : all) cudaEventDestroy(e);
+    }
+};
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -777,13 +796,15 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         F[i] = Z[i] - T * r > 0 ? Z[i] - T * r : 0;
     }
     Z[C] = F[C] = n;
+    Events events;
     std::vector<cudaEvent_t> up(C), done(C);
     cudaEvent_t ev[4];
-    for (auto& e : ev) CU_TRY(cudaEventCreate(&e));
+    for (auto& e : ev) e = events.make(cudaEventDefault);
     for (int i = 0; i < C; ++i) {
-        CU_TRY(cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
-        CU_TRY(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+        up[i] = events.make();
+        done[i] = events.make();
     }
+    CU_TRY(events.err);
     CU_TRY(cudaEventRecord(ev[0], st));
     CU_TRY(cudaStreamWaitEvent(S.st_in, ev[0], 0));
     // upload chunk i = padded outer indices [U_i, U_i+1)
@@ -809,8 +830,9 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) < 1 ? 1 : (atoi(e) > 4 ? 4 : atoi(e));
     const size_t nb = blocks.size();
     std::vector<cudaEvent_t> unpacked(C), bd((size_t)C * nb);
-    for (auto& e : unpacked) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    for (auto& e : bd) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : unpacked) e = events.make();
+    for (auto& e : bd) e = events.make();
+    CU_TRY(events.err);
     for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
     bool first_download = false;
     for (int i = 0; i < C; ++i) {
@@ -868,13 +890,6 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         timing->kernel = c.kernel;
         timing->result_in_out = (int)(desc->iterations & 1u);
     }
-    for (auto& e : ev) cudaEventDestroy(e);
-    for (int i = 0; i < C; ++i) {
-        cudaEventDestroy(up[i]);
-        cudaEventDestroy(done[i]);
-        cudaEventDestroy(unpacked[i]);
-    }
-    for (auto& e : bd) cudaEventDestroy(e);
     return SB200_OK;
 }
 
@@ -976,8 +991,10 @@ int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* ti
         if (C > 1) return run_host_pipelined(desc, c, in, out, timing, C);
     }
     cudaStream_t st = 0;
+    Events events;
     cudaEvent_t ev[4];
-    for (auto& e : ev) CU_TRY(cudaEventCreate(&e));
+    for (auto& e : ev) e = events.make(cudaEventDefault);
+    CU_TRY(events.err);
     CU_TRY(cudaEventRecord(ev[0], st));
     // Both reference buffers carry the same Dirichlet halo by construction
     // (Stencil::generate_initialized_matrix, stencil.cpp:190-207): upload `in` once and
@@ -1027,7 +1044,6 @@ int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* ti
         timing->kernel = used_kernel;
         timing->result_in_out = (int)(desc->iterations & 1u);
     }
-    for (auto& e : ev) cudaEventDestroy(e);
     return SB200_OK;
 }
 
