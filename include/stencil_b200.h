@@ -44,11 +44,13 @@ typedef enum sb200_kernel {
     SB200_KERNEL_GENERIC = 1, /* one step per launch, any ndim/shape/radius   */
     SB200_KERNEL_WARP2D = 2,  /* 2-D r=1 (star/box) and r=2..4 (star): register/shuffle temporal blocking */
     SB200_KERNEL_TMA3D = 3,   /* 3-D r=1, TMA-staged z-streaming, temporal blk */
-    SB200_KERNEL_RESIDENT2D = 4 /* small 2-D r=1 grids: register-resident in one
+    SB200_KERNEL_RESIDENT2D = 4, /* small 2-D r=1 grids: register-resident in one
                                    thread-block cluster for ALL steps of a call, one
                                    launch (the analogue of the reference's RMA kernel,
                                    stencil_rma.cpp:333-458); AUTO picks it for
                                    single-GPU calls of >= 16 steps when the grid fits */
+    SB200_KERNEL_LINE1D = 5     /* 1-D star/box r=1..4: a warp keeps 512 points in registers,
+                                   up to 16 fused steps per launch */
 } sb200_kernel;
 
 /* Problem descriptor.  Replaces the reference's `Arguments{block_size,
@@ -221,6 +223,7 @@ int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLA
  *   TMA3D:      tiles_x x tiles_y xy tiles, `chunks` z chunks of `chunk_extent` planes
  *   WARP2D:     tiles_x strips of 128 columns, `chunks` row chunks of `chunk_extent` rows
  *   RESIDENT2D: tiles_x x tiles_y warp tiles of 128 x chunk_extent points on `chunks` CTAs
+ *   LINE1D:     tiles_x warp segments storing `chunk_extent` of their 512 points each
  *   GENERIC:    all zero */
 typedef struct sb200_plan_info {
     int32_t kernel;           /* sb200_kernel family */

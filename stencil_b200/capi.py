@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libstencil_b200.so")
 STAR, BOX = 0, 1
 F32, F64 = 0, 1
 INIT_REF, INIT_RANDOM = 0, 1
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_WARP2D, KERNEL_TMA3D, KERNEL_RESIDENT2D = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_WARP2D, KERNEL_TMA3D, KERNEL_RESIDENT2D, KERNEL_LINE1D = 0, 1, 2, 3, 4, 5
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE = 0, -1, -2, -3, -4
 
 # every symbol include/stencil_b200.h declares

@@ -22,6 +22,7 @@
 #include "util_kernels.cuh"
 #include "warp2d.cuh"
 #include "warp2dr.cuh"
+#include "line1d.cuh"
 
 using namespace sb200;
 
@@ -110,7 +111,7 @@ int validate(const sb200_desc* d) {
         if (a >= d->ndim && d->n[a] > 1) return fail(SB200_ERR_INVALID, "n[%d] must be 1 for ndim=%d", a, d->ndim);
         if (d->n[a] > (1ull << 40)) return fail(SB200_ERR_INVALID, "n[%d] too large", a);
     }
-    if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_RESIDENT2D)
+    if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_LINE1D)
         return fail(SB200_ERR_INVALID, "bad kernel selector %d", d->kernel);
     return SB200_OK;
 }
@@ -257,16 +258,18 @@ Choice choose(const sb200_desc* d) {
     Choice c;
     const bool w2d_ok = warp2d_supports(d);
     const bool t3_ok = d->ndim == 3 && d->radius == 1;
+    const bool l1_ok = d->ndim == 1 && d->radius <= 4;
     int kern = d->kernel;
     if (kern == SB200_KERNEL_AUTO)
-        kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : SB200_KERNEL_GENERIC;
+        kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : l1_ok ? SB200_KERNEL_LINE1D : SB200_KERNEL_GENERIC;
     c.kernel = kern;
     c.max_k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? w2r_max_k((int)d->radius, (int)esize(d->dtype)) : W2D_MAXK)
               : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
-              : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30) : 1;
+              : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30)
+              : kern == SB200_KERNEL_LINE1D ? L1D_MAXK : 1;
     int k = (int)d->time_block;
     if (kern == SB200_KERNEL_RESIDENT2D) k = c.max_k;  // the whole call is one launch
-    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? c.max_k : 4) : kern == SB200_KERNEL_TMA3D ? 2 : 1;
+    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? c.max_k : 4) : kern == SB200_KERNEL_LINE1D ? l1d_default_k((int)d->radius) : kern == SB200_KERNEL_TMA3D ? 2 : 1;
     if (k > c.max_k) k = c.max_k;
     c.k = k;
     return c;
@@ -275,6 +278,8 @@ Choice choose(const sb200_desc* d) {
 int check_choice(const sb200_desc* d, const Choice& c) {
     if (c.kernel == SB200_KERNEL_WARP2D && !warp2d_supports(d))
         return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2 and radius=1 (star or box) or radius 2..4 (star)");
+    if (c.kernel == SB200_KERNEL_LINE1D && !(d->ndim == 1 && d->radius <= 4))
+        return fail(SB200_ERR_UNSUPPORTED, "LINE1D kernel needs ndim=1, radius 1..4");
     if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
         return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1");
     if (c.kernel == SB200_KERNEL_RESIDENT2D &&
@@ -301,6 +306,9 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
+        case SB200_KERNEL_LINE1D:
+            CU_TRY(launch_line1d<T>(a, b, g, d->shape, k, st));
+            return SB200_OK;
     }
     return fail(SB200_ERR_INVALID, "kernel family %d cannot run a partial pass", c.kernel);
 }
@@ -489,6 +497,12 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
         info->tiles_y = (uint32_t)p.nty;
         info->chunks = (uint32_t)p.nchunks;
         info->chunk_extent = (uint32_t)p.chunk_planes;
+    } else if (c.kernel == SB200_KERNEL_LINE1D) {
+        const L1dPlan p = l1d_plan(g.n[0], k, g.r);
+        info->tiles_x = (uint32_t)p.nseg;
+        info->tiles_y = 1;
+        info->chunks = 1;
+        info->chunk_extent = (uint32_t)p.valid;
     }
     sb200_desc d2 = *desc;
     d2.iterations = steps;

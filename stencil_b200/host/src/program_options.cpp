@@ -34,7 +34,7 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
     app.option("--time-block", result.time_block, "Fused time steps per HBM round trip (0 = auto).", 0u);
     app.option("--init", result.init, "Initial condition: ref or random.", std::string("ref"));
     app.option("--seed", result.seed, "Seed of the random initial condition.", 1ull);
-    app.option("--kernel", result.kernel, "CUDA kernel family: auto, generic, warp2d, tma3d, resident2d.", std::string("auto"));
+    app.option("--kernel", result.kernel, "CUDA kernel family: auto, generic, warp2d, tma3d, resident2d, line1d.", std::string("auto"));
     app.option("--json", result.json_path, "Append one JSON record per method to this file.");
     app.option("--bmp", result.bmp_path, "Write the final 2-D field as a BMP heat map.");
 
@@ -60,8 +60,8 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
         if (!one_of(result.dtype, {"f32", "f64"})) throw cli::ParseError("--dtype must be f32 or f64", 105);
         if (!one_of(result.stencil, {"star", "box"})) throw cli::ParseError("--stencil must be star or box", 105);
         if (!one_of(result.init, {"ref", "random"})) throw cli::ParseError("--init must be ref or random", 105);
-        if (!one_of(result.kernel, {"auto", "generic", "warp2d", "tma3d", "resident2d"}))
-            throw cli::ParseError("--kernel must be auto, generic, warp2d, tma3d or resident2d", 105);
+        if (!one_of(result.kernel, {"auto", "generic", "warp2d", "tma3d", "resident2d", "line1d"}))
+            throw cli::ParseError("--kernel must be auto, generic, warp2d, tma3d, resident2d or line1d", 105);
         if (result.radius == 0) throw cli::ParseError("--radius must be at least 1", 105);
         if (result.repeat_count == 0) throw cli::ParseError("--repeat must be at least 1", 105);
         if (result.shape.empty() && result.matrix_size == 0) throw cli::ParseError("--matrix-size must be positive", 105);

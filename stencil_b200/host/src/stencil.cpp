@@ -108,6 +108,7 @@ sb200_desc make_desc(ProgramOptions const& o) {
                : o.kernel == "warp2d" ? SB200_KERNEL_WARP2D
                : o.kernel == "tma3d"  ? SB200_KERNEL_TMA3D
                : o.kernel == "resident2d" ? SB200_KERNEL_RESIDENT2D
+               : o.kernel == "line1d" ? SB200_KERNEL_LINE1D
                                       : SB200_KERNEL_AUTO;
     return d;
 }

@@ -26,7 +26,7 @@ import ctypes
 from . import capi
 
 _KERNEL_NAMES = {capi.KERNEL_GENERIC: "generic", capi.KERNEL_WARP2D: "warp2d",
-                 capi.KERNEL_TMA3D: "tma3d"}
+                 capi.KERNEL_TMA3D: "tma3d", capi.KERNEL_LINE1D: "line1d"}
 
 
 def resolve_kernel(desc: capi.Desc):
@@ -35,15 +35,17 @@ def resolve_kernel(desc: capi.Desc):
     star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
     w2d = desc.ndim == 2 and (desc.radius == 1 or star_r)
     t3 = desc.ndim == 3 and desc.radius == 1
+    l1 = desc.ndim == 1 and desc.radius <= 4
     kern = desc.kernel
     if kern == capi.KERNEL_AUTO:
-        kern = capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3 else capi.KERNEL_GENERIC
+        kern = (capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3
+                else capi.KERNEL_LINE1D if l1 else capi.KERNEL_GENERIC)
     d = capi.Desc.from_buffer_copy(desc)
     d.kernel = kern
     max_k = int(capi.lib().sb200_max_time_block(ctypes.byref(d)))
     if max_k < 1:
         raise capi.StencilError(max_k, capi.lib().sb200_last_error().decode())
-    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_TMA3D: 2,
+    k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_TMA3D: 2, capi.KERNEL_LINE1D: min(16, 32 // max(1, desc.radius)),
                             capi.KERNEL_WARP2D: 4 if desc.radius == 1 else max_k}[kern]
     return kern, min(k, max_k)
 

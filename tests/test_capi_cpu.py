@@ -99,8 +99,15 @@ def test_plan_host_logic(monkeypatch):
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 1, 100)
     assert capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     assert capi.plan(capi.make_desc((400, 400), 5, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    # 1-D: warp segments of 512 points; 16 fused steps by default at r=1 (10 here: one launch,
+    # 512 - 12 - 10 -> 488 stored per segment), 8 at r=4
     p = capi.plan(capi.make_desc((1 << 20,), 1, capi.STAR, capi.F64, 10), 10)
-    assert (p.kernel, p.launches, p.pipeline_chunks) == (capi.KERNEL_GENERIC, 10, 1)
+    assert (p.kernel, p.time_block, p.launches, p.pipeline_chunks) == (capi.KERNEL_LINE1D, 16, 1, 1)
+    assert p.chunk_extent == 488 and p.tiles_x == -(-(1 << 20) // 488)
+    p = capi.plan(capi.make_desc((1 << 20,), 4, capi.BOX, capi.F32, 100), 100)
+    assert (p.kernel, p.time_block, p.launches, p.chunk_extent) == (capi.KERNEL_LINE1D, 8, 13, 448)
+    p = capi.plan(capi.make_desc((1 << 20,), 5, capi.STAR, capi.F64, 10), 10)
+    assert (p.kernel, p.launches) == (capi.KERNEL_GENERIC, 10)
     # T*r too long for the grid: the last parallelogram cannot start inside it -> not pipelined
     p = capi.plan(capi.make_desc((512, 512, 512), 1, capi.STAR, capi.F64, 600), 600)
     assert p.pipeline_chunks == 1

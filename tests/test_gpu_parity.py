@@ -88,6 +88,19 @@ def test_warp2d_radius_kernel(gpu, n, r, T, k, dtype):
     assert t.kernel == capi.KERNEL_WARP2D and t.time_block == ke and t.launches == -(-T // ke)
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
+@pytest.mark.parametrize("n,r,T,k", [
+    (1, 1, 3, 2), (3, 2, 5, 8), (37, 1, 4, 0), (509, 1, 20, 8), (512, 4, 9, 4), (1000, 3, 5, 5),
+    (4099, 2, 33, 16), (100003, 1, 24, 0), (65536, 4, 16, 16), (20000, 3, 7, 1), (497, 1, 8, 8),
+])
+def test_line1d_kernel(gpu, n, r, T, k, shape, dtype):
+    """1-D grids: K steps fused in registers per warp segment, bit-exact for any K."""
+    t = _check((n,), r, shape, dtype, T, time_block=k)
+    ke = min(k or min(16, 32 // r), 16)
+    assert t.kernel == capi.KERNEL_LINE1D and t.time_block == ke and t.launches == -(-T // ke)
+
+
 def test_warp2d_radius_box_is_unsupported(gpu):
     d = capi.make_desc((64, 64), radius=2, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
     a = np.zeros((68, 68), np.float32)
@@ -122,6 +135,8 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 5, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((3000,), 2, capi.BOX, np.float64, 9).kernel == capi.KERNEL_LINE1D
+    assert _check((3000,), 6, capi.STAR, np.float32, 3).kernel == capi.KERNEL_GENERIC
 
 
 def test_ref_init_denormals_preserved(gpu):

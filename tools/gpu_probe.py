@@ -72,3 +72,9 @@ if "rad" in which:  # general-radius 2-D star: fused warp kernel vs the one-thre
                         capi.make_desc((8192, 8192), r, capi.STAR, dt, 24, kernel=capi.KERNEL_WARP2D))):
                     run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 24, capi.KERNEL_WARP2D, k, r=r)
             run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 8, capi.KERNEL_GENERIC, 1, r=r)
+if "line" in which:  # 1-D: fused register kernel vs one launch per step
+    for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
+        for r in (1, 4):
+            for k in (1, 4, 8, 16):
+                run(f"1d-r{r}-{nm}", (1 << 27,), capi.STAR, dt, 48, capi.KERNEL_LINE1D, k, r=r)
+            run(f"1d-r{r}-{nm}", (1 << 27,), capi.STAR, dt, 8, capi.KERNEL_GENERIC, 1, r=r)
