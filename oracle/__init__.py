@@ -139,3 +139,34 @@ def ref_naive_2d_f32(N: int, r: int, T: int) -> np.ndarray:
     if R.ref_naive_2d_f32(N, r, T, out.ctypes.data) != 0:
         raise RuntimeError("reference probe protocol failed")
     return out
+
+
+_ref64 = None
+
+
+def ref64_lib():
+    """The reference's own sources compiled with float -> double (oracle/Makefile:
+    _ref/libref64.so), or None if absent."""
+    global _ref64
+    if _ref64 is None:
+        path = os.path.join(_HERE, "_ref", "libref64.so")
+        if not os.path.exists(path):
+            return None
+        R = ctypes.CDLL(path)
+        R.ref_naive_2d_f64.restype = ctypes.c_int
+        R.ref_naive_2d_f64.argtypes = [ctypes.c_uint] * 3 + [ctypes.c_void_p]
+        R.ref_check_2d_f64.restype = ctypes.c_int
+        R.ref_check_2d_f64.argtypes = [ctypes.c_uint] * 3 + [ctypes.c_void_p]
+        _ref64 = R
+    return _ref64
+
+
+def ref_naive_2d_f64(N: int, r: int, T: int) -> np.ndarray:
+    """Interior N×N result of the reference naive loop compiled at double precision."""
+    R = ref64_lib()
+    if R is None:
+        raise RuntimeError("oracle/_ref/libref64.so not built (needs /root/reference)")
+    out = np.empty((N, N), dtype=np.float64)
+    if R.ref_naive_2d_f64(N, r, T, out.ctypes.data) != 0:
+        raise RuntimeError("reference probe protocol failed")
+    return out

@@ -25,4 +25,12 @@ namespace std {
 int sb200_ref_capture(const char* fmt, ...);
 }
 #define printf sb200_ref_capture
+/* SB200_REF_F64: the same reference sources at double precision.  Every std header the
+ * reference includes is already in (guards above), so this one-token substitution only
+ * touches the reference's own `float` (stencil.hpp:49-51, stencil.cpp:85-86,103): the loop
+ * nest, the order of the adds and `sum * avg` are the reference's; `1.f / double(...)` and
+ * `0.f` promote exactly. */
+#ifdef SB200_REF_F64
+#define float double
+#endif
 #endif

@@ -9,6 +9,14 @@
 #include <cstdarg>
 #include <cstdio>
 #include <vector>
+#ifdef SB200_REF_F64
+// double-precision build of the same reference sources (see hook.h); exported under _f64 names
+#include "hook.h"
+#undef printf
+#define ref_naive_2d_f32 ref_naive_2d_f64
+#define ref_check_2d_f32 ref_check_2d_f64
+#define ref_time_check_2d_f32 ref_time_check_2d_f64
+#endif
 
 #define private public  // reach Stencil::matrix / result / options (stencil.hpp:46-51)
 #include <stencil/stencil.hpp>

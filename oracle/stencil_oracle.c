@@ -10,7 +10,10 @@
  * Parity status:
  *   2-D star f32, any radius : PINNED — bit-compared against the reference's own
  *       check_result compiled from /root/reference (oracle/ref_shim, tests/golden/).
- *   f64, 1-D, 3-D, box       : "parity unpinned" — the reference has no such code;
+ *   2-D star f64, any radius : pinned against the SAME reference sources compiled with
+ *       float -> double (oracle/Makefile: _ref/libref64.so; tests/golden/ref_2d_f64.npz) —
+ *       the reference's loop nest and add order, at a precision it does not ship.
+ *   1-D, 3-D, box            : "parity unpinned" — the reference has no such code;
  *       this file is the definition.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference

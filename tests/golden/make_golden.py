@@ -1,4 +1,4 @@
-"""Generate tests/golden/ref_2d_f32.npz from the GENUINE reference naive loop.
+"""Generate tests/golden/ref_2d_f32.npz (and ref_2d_f64.npz) from the GENUINE reference naive loop.
 
 Runs only where /root/reference is mounted (the build container): oracle/_ref/libref.so
 is the reference's own src/stencil/stencil.cpp compiled by oracle/Makefile, and
@@ -23,6 +23,13 @@ CASES = [
     (64, 1, 100), (64, 2, 16), (64, 1, 1000),
 ]
 
+# fp64: radius 3 (avg = 1/12 is not a dyadic rational) and long runs are where double and
+# float arithmetic part ways
+CASES64 = [
+    (1, 1, 1), (3, 1, 2), (5, 2, 4), (13, 1, 9), (16, 1, 33), (24, 2, 7), (32, 3, 5), (40, 4, 9),
+    (48, 3, 50), (64, 1, 100), (64, 3, 16), (64, 1, 1000),
+]
+
 if __name__ == "__main__":
     oracle.build()
     out = {}
@@ -30,3 +37,9 @@ if __name__ == "__main__":
         out[f"N{N}_r{r}_T{T}"] = oracle.ref_naive_2d_f32(N, r, T)
         print(N, r, T, "%.15f" % out[f"N{N}_r{r}_T{T}"][0, 0])
     np.savez_compressed(os.path.join(os.path.dirname(__file__), "ref_2d_f32.npz"), **out)
+    # the same reference sources compiled with float -> double (oracle/Makefile: libref64.so)
+    out64 = {}
+    for N, r, T in CASES64:
+        out64[f"N{N}_r{r}_T{T}"] = oracle.ref_naive_2d_f64(N, r, T)
+        print("f64", N, r, T, "%.17g" % out64[f"N{N}_r{r}_T{T}"][0, 0])
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "ref_2d_f64.npz"), **out64)

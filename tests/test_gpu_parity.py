@@ -47,6 +47,18 @@ def test_reference_golden_2d_f32(gpu, key):
     assert np.array_equal(oracle.interior(got, r).view(np.uint32), GOLD[key].view(np.uint32))
 
 
+GOLD64 = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_2d_f64.npz"))
+
+
+@pytest.mark.parametrize("key", sorted(GOLD64.files))
+def test_reference_golden_2d_f64(gpu, key):
+    """CUDA path vs the reference's loop compiled at double precision (bit-exact)."""
+    N, r, T = (int(p[1:]) for p in key.split("_"))
+    a, b = _oracle_pair((N, N), r, np.float64, 0)
+    got, _ = sweep.run_host((N, N), a, b, T, radius=r)
+    assert np.array_equal(oracle.interior(got, r).view(np.uint64), GOLD64[key].view(np.uint64))
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
 @pytest.mark.parametrize("n,r,T", [

@@ -3,6 +3,8 @@
 Golden grids in tests/golden/ref_2d_f32.npz were produced by the GENUINE reference naive
 loop (Stencil::check_result, /root/reference/src/stencil/stencil.cpp:75-131) via
 tests/golden/make_golden.py.  Known answers are the ones SURVEY.md §8(c) lists.
+tests/golden/ref_2d_f64.npz is the same reference source compiled with float -> double
+(oracle/Makefile: _ref/libref64.so): the reference's loop nest and add order at fp64.
 """
 import os
 
@@ -24,6 +26,23 @@ def test_oracle_matches_reference_golden_bitwise(key):
     N, r, T = _case(key)
     got = oracle.interior(oracle.run((N, N), r, oracle.STAR, T), r)
     assert np.array_equal(got.view(np.uint32), GOLD[key].view(np.uint32))
+
+
+GOLD64 = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_2d_f64.npz"))
+
+
+@pytest.mark.parametrize("key", sorted(GOLD64.files))
+def test_oracle_matches_reference_golden_f64_bitwise(key):
+    N, r, T = _case(key)
+    got = oracle.interior(oracle.run((N, N), r, oracle.STAR, T, dtype=oracle.F64), r)
+    assert got.dtype == np.float64
+    assert np.array_equal(got.view(np.uint64), GOLD64[key].view(np.uint64))
+
+
+def test_f64_golden_is_not_the_f32_grid():
+    """The fp64 fixture really is double arithmetic: it differs from the fp32 grid where
+    avg = 1/(4r) is not a dyadic rational."""
+    assert np.abs(GOLD64["N32_r3_T5"] - GOLD["N32_r3_T5"].astype(np.float64)).max() > 0
 
 
 KNOWN = [  # (N, r, T, element (0,0)) from the reference loop, SURVEY.md §8(c)
