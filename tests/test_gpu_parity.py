@@ -297,3 +297,64 @@ def test_pipelined_host_path(gpu, monkeypatch, chunks, n, r, shape, dtype, T, k,
     monkeypatch.setenv("SB200_PIPELINE_CHUNKS", "1")
     t1 = _check(n, r, shape, dtype, T, time_block=k, kernel=kernel)
     assert t1.launches == blocks
+
+
+@pytest.mark.parametrize("n,r,shape,dtype,T,k,kernel", [
+    ((96, 80, 40), 1, capi.STAR, np.float64, 7, 2, capi.KERNEL_TMA3D),
+    ((70, 66, 33), 1, capi.BOX, np.float32, 5, 2, capi.KERNEL_TMA3D),
+    ((300, 90), 1, capi.BOX, np.float32, 13, 4, capi.KERNEL_WARP2D),
+    ((257, 120), 1, capi.STAR, np.float64, 16, 8, capi.KERNEL_WARP2D),
+    ((200, 150), 2, capi.STAR, np.float32, 9, 4, capi.KERNEL_WARP2D),   # radius kernels: ghost = r*k rows
+    ((130, 140), 3, capi.STAR, np.float64, 5, 2, capi.KERNEL_WARP2D),
+    ((150, 101), 4, capi.STAR, np.float32, 4, 2, capi.KERNEL_WARP2D),
+    ((64, 48, 30), 2, capi.STAR, np.float64, 3, 1, capi.KERNEL_GENERIC),
+    ((120, 90), 3, capi.BOX, np.float32, 4, 1, capi.KERNEL_GENERIC),
+])
+def test_two_slabs_on_one_gpu(gpu, n, r, shape, dtype, T, k, kernel):
+    """The slab path's kernels (ghost planes/rows that are ordinary updatable points, update
+    domain open on the internal face) without a second GPU: the grid is cut in two along the
+    outermost axis, each slab is swept k steps at a time through sb200_sweep_device with
+    ghost = r*k, and the ghosts are refreshed from the other slab on the host in between.
+    Same bits as the single-grid oracle."""
+    code = oracle.F64 if dtype == np.float64 else oracle.F32
+    a = oracle.fill(n, r, code, oracle.INIT_RANDOM, 9)
+    b = oracle.fill(n, r, code, oracle.INIT_REF)
+    G = a.copy()
+    want = b if oracle.sweep(n, r, shape, T, a, b, threads=oracle.max_threads()) else a
+    nz = n[-1]
+    cuts = [0, nz // 2 + 1, nz]
+    g = r * k
+    slabs = []
+    for s in range(2):
+        ns = tuple(n[:-1]) + (cuts[s + 1] - cuts[s],)
+        d = capi.make_desc(ns, r, shape, capi.F64 if dtype == np.float64 else capi.F32, T,
+                           time_block=k, kernel=kernel)
+        slabs.append((d, sweep.DeviceGrids(d, ghost=g), ns))
+
+    def scatter(s):
+        """Host image of slab s (halo + ghost + interior + ghost + halo) cut out of G."""
+        d, dg, ns = slabs[s]
+        S = np.zeros((ns[-1] + 2 * (r + g),) + G.shape[1:], dtype)
+        for p in range(S.shape[0]):
+            zg = r + cuts[s] + (p - (r + g))  # padded index into G
+            if 0 <= zg < G.shape[0]:
+                S[p] = G[zg]
+        return S
+
+    done = 0
+    while done < T:
+        kk = min(k, T - done)
+        for s in range(2):
+            d, dg, ns = slabs[s]
+            S = scatter(s)
+            dg.upload(S, 0)
+            dg.upload(S, 1)
+            dg.cur = 0
+            nl = dg.sweep(kk, lo_boundary=int(s == 0), hi_boundary=int(s == 1))
+            assert nl == 1
+        for s in range(2):
+            d, dg, ns = slabs[s]
+            R = dg.download()
+            G[r + cuts[s]:r + cuts[s + 1]] = R[r + g:r + g + ns[-1]]
+        done += kk
+    assert np.array_equal(G.view(np.uint8), want.view(np.uint8))
