@@ -45,28 +45,11 @@ __device__ __forceinline__ void l1d_store4(double* p, const double (&v)[4]) {
     reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
 }
 
-template <class T, int SHAPE, int R>
-__global__ void __launch_bounds__(32 * L1D_WARPS)
-sweep_line1d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, int K, int HL, int V,
-                    long long nseg, T avg) {
+// K time steps on a warp's register-resident segment.  EDGE: some points lie outside [0, n)
+// and pass through (bit 4j+i of upd clear).
+template <class T, int SHAPE, int R, bool EDGE>
+__device__ __forceinline__ void l1d_steps(T (&v)[L1D_J][4], unsigned upd, int K, int lane, T avg) {
     constexpr unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const long long seg = (long long)blockIdx.x * L1D_WARPS + (threadIdx.x >> 5);
-    if (seg >= nseg) return;
-    const long long x0 = seg * V - HL;  // first point of the segment (a multiple of 4)
-    T v[L1D_J][4];
-    unsigned upd = 0;  // bit 4j+i: point i of chunk j lies in [0, n)
-#pragma unroll
-    for (int j = 0; j < L1D_J; ++j) {
-        const long long gx = x0 + j * 128 + lane * 4;
-        // stay inside the allocation; clamped lanes hold points nothing valid depends on
-        long long gl = gx < -(long long)g.ox ? -(long long)g.ox : gx;
-        if (gl + 4 > g.pitch_x - g.ox) gl = g.pitch_x - g.ox - 4;
-        l1d_load4(in + g.ox + gl, v[j]);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (gx + i >= 0 && gx + i < g.n[0]) upd |= 1u << (4 * j + i);
-    }
     const int from_left = (lane + 31) & 31, from_right = (lane + 1) & 31;
 #pragma unroll 1
     for (int s = 0; s < K; ++s) {
@@ -99,7 +82,7 @@ sweep_line1d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, int K
 #pragma unroll
                     for (int k = -R; k <= R; ++k) sum = add_rn(sum, w[R + i + k]);
                 }
-                o[j][i] = ((upd >> (4 * j + i)) & 1u) ? mul_rn(sum, avg) : v[j][i];
+                o[j][i] = (!EDGE || ((upd >> (4 * j + i)) & 1u)) ? mul_rn(sum, avg) : v[j][i];
             }
         }
 #pragma unroll
@@ -107,6 +90,36 @@ sweep_line1d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, int K
 #pragma unroll
             for (int i = 0; i < 4; ++i) v[j][i] = o[j][i];
     }
+}
+
+template <class T, int SHAPE, int R>
+__global__ void __launch_bounds__(32 * L1D_WARPS)
+sweep_line1d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, int K, int HL, int V,
+                    long long nseg, T avg) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const long long seg = (long long)blockIdx.x * L1D_WARPS + (threadIdx.x >> 5);
+    if (seg >= nseg) return;
+    const long long x0 = seg * V - HL;  // first point of the segment (a multiple of 4)
+    T v[L1D_J][4];
+    unsigned upd = 0;  // bit 4j+i: point i of chunk j lies in [0, n)
+#pragma unroll
+    for (int j = 0; j < L1D_J; ++j) {
+        const long long gx = x0 + j * 128 + lane * 4;
+        // stay inside the allocation; clamped lanes hold points nothing valid depends on
+        long long gl = gx < -(long long)g.ox ? -(long long)g.ox : gx;
+        if (gl + 4 > g.pitch_x - g.ox) gl = g.pitch_x - g.ox - 4;
+        l1d_load4(in + g.ox + gl, v[j]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (gx + i >= 0 && gx + i < g.n[0]) upd |= 1u << (4 * j + i);
+    }
+    // interior segments (every point of the warp updatable) skip the pass-through selects,
+    // which otherwise cost as many issue slots as the arithmetic
+    if (__all_sync(FULL, upd == 0xffffu))
+        l1d_steps<T, SHAPE, R, false>(v, upd, K, lane, avg);
+    else
+        l1d_steps<T, SHAPE, R, true>(v, upd, K, lane, avg);
 #pragma unroll
     for (int j = 0; j < L1D_J; ++j) {
         const int c = j * 128 + lane * 4;  // segment-relative
