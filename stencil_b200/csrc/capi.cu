@@ -774,8 +774,8 @@ static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, 
 // right edge of parallelogram i at time level t stays in the ping-pong buffer of that parity
 // (later blocks of i write strictly below it, because block sizes never decrease), which is
 // exactly the halo parallelogram i+1 needs: no extra storage, same kernels, same bits.
-static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
-                              sb200_timing* timing, int C) {
+static int run_host_pipelined_impl(const sb200_desc* desc, const Choice& c, void* in, void* out,
+                                   sb200_timing* timing, int C) {
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t es = esize(desc->dtype);
@@ -905,6 +905,15 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         timing->result_in_out = (int)(desc->iterations & 1u);
     }
     return SB200_OK;
+}
+
+static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
+                              sb200_timing* timing, int C) {
+    const int rc = run_host_pipelined_impl(desc, c, in, out, timing, C);
+    // an error return may leave copies and launches in flight on the internal streams that
+    // still use the caller's host buffers: drain them before handing control back
+    if (rc != SB200_OK) cudaDeviceSynchronize();
+    return rc;
 }
 
 int sb200_upload(const sb200_desc* desc, uint32_t ghost, const void* host, void* dev, void* stream) {
