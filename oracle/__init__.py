@@ -170,3 +170,37 @@ def ref_naive_2d_f64(N: int, r: int, T: int) -> np.ndarray:
     if R.ref_naive_2d_f64(N, r, T, out.ctypes.data) != 0:
         raise RuntimeError("reference probe protocol failed")
     return out
+
+
+_emu = None
+EMU_METHODS = ("DMA", "DMASlavePack", "RMA")
+
+
+def ref_emu_lib():
+    """The reference's accelerator kernels on the athread emulator (oracle/Makefile:
+    _ref/libref_emu.so, oracle/ref_shim/emu/), or None if absent."""
+    global _emu
+    if _emu is None:
+        path = os.path.join(_HERE, "_ref", "libref_emu.so")
+        if not os.path.exists(path):
+            return None
+        R = ctypes.CDLL(path)
+        R.ref_emu_run_2d_f32.restype = ctypes.c_int
+        R.ref_emu_run_2d_f32.argtypes = [ctypes.c_char_p] + [ctypes.c_uint] * 4 + \
+            [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        _emu = R
+    return _emu
+
+
+def ref_emu_run_2d_f32(method: str, N: int, block: int, r: int, T: int):
+    """Interior N×N result of the reference's own DMA / DMASlavePack / RMA kernel
+    (src/stencil/slave/*.cpp) run on the emulated 8x8 CPE array, and the reference's own
+    check_result() verdict on it.  N must be 8 * block."""
+    R = ref_emu_lib()
+    if R is None:
+        raise RuntimeError("oracle/_ref/libref_emu.so not built (needs /root/reference)")
+    out = np.empty((N, N), dtype=np.float32)
+    ok = ctypes.c_int(-1)
+    if R.ref_emu_run_2d_f32(method.encode(), N, block, r, T, out.ctypes.data, ctypes.byref(ok)) != 0:
+        raise ValueError(f"emulated reference kernel cannot run {method} N={N} block={block} r={r} T={T}")
+    return out, bool(ok.value)

@@ -13,6 +13,9 @@
  *   2-D star f64, any radius : pinned against the SAME reference sources compiled with
  *       float -> double (oracle/Makefile: _ref/libref64.so; tests/golden/ref_2d_f64.npz) —
  *       the reference's loop nest and add order, at a precision it does not ship.
+ *       Also held, within tolerance (another add order), against grids from the reference's own
+ *       DMA / DMASlavePack / RMA kernels run on the athread emulator (oracle/ref_shim/emu/,
+ *       tests/golden/ref_emu_2d_f32.npz).
  *   1-D, 3-D, box            : "parity unpinned" — the reference has no such code;
  *       this file is the definition.
  *

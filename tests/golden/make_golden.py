@@ -1,4 +1,5 @@
-"""Generate tests/golden/ref_2d_f32.npz (and ref_2d_f64.npz) from the GENUINE reference naive loop.
+"""Generate tests/golden/ref_2d_f32.npz (and ref_2d_f64.npz) from the GENUINE reference naive loop,
+and ref_emu_2d_f32.npz from the reference's accelerator kernels run on the athread emulator.
 
 Runs only where /root/reference is mounted (the build container): oracle/_ref/libref.so
 is the reference's own src/stencil/stencil.cpp compiled by oracle/Makefile, and
@@ -30,6 +31,15 @@ CASES64 = [
     (48, 3, 50), (64, 1, 100), (64, 3, 16), (64, 1, 1000),
 ]
 
+# The reference's ACCELERATOR kernels on the athread emulator (oracle/ref_shim/emu/):
+# (method, N = 8*block, radius, T).  Block sizes from run_expr.py's sweep (8 .. 120); only
+# the DMA kernel takes a radius (stencil_dma_slave_pack.cpp:380-382, stencil_rma.cpp:466-471).
+CASES_EMU = [
+    ("DMA", 64, 1, 1), ("DMA", 64, 1, 100), ("DMA", 64, 2, 9), ("DMA", 128, 3, 16), ("DMA", 128, 4, 7),
+    ("DMA", 256, 1, 200), ("DMASlavePack", 64, 1, 33), ("DMASlavePack", 128, 1, 100),
+    ("RMA", 64, 1, 10), ("RMA", 64, 1, 1000), ("RMA", 192, 1, 101),
+]
+
 if __name__ == "__main__":
     oracle.build()
     out = {}
@@ -43,3 +53,11 @@ if __name__ == "__main__":
         out64[f"N{N}_r{r}_T{T}"] = oracle.ref_naive_2d_f64(N, r, T)
         print("f64", N, r, T, "%.17g" % out64[f"N{N}_r{r}_T{T}"][0, 0])
     np.savez_compressed(os.path.join(os.path.dirname(__file__), "ref_2d_f64.npz"), **out64)
+    # the reference's own DMA / DMASlavePack / RMA kernels, emulated CPE array
+    emu = {}
+    for m, N, r, T in CASES_EMU:
+        g, ok = oracle.ref_emu_run_2d_f32(m, N, N // 8, r, T)
+        assert ok, "the reference's own check_result rejected its kernel"
+        emu[f"{m}_N{N}_r{r}_T{T}"] = g
+        print(m, N, r, T, "%.15f" % g[0, 0])
+    np.savez_compressed(os.path.join(os.path.dirname(__file__), "ref_emu_2d_f32.npz"), **emu)

@@ -59,6 +59,28 @@ def test_reference_golden_2d_f64(gpu, key):
     assert np.array_equal(oracle.interior(got, r).view(np.uint64), GOLD64[key].view(np.uint64))
 
 
+GOLD_EMU = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_emu_2d_f32.npz"))
+
+
+@pytest.mark.parametrize("key", sorted(GOLD_EMU.files))
+def test_reference_accelerator_kernels_2d_f32(gpu, key):
+    """CUDA path vs grids produced by the reference's OWN accelerator kernels (DMA /
+    DMASlavePack / RMA, src/stencil/slave/*.cpp) run on the athread emulator.  Those kernels
+    add in another order than the reference's naive loop (stencil_dma.cpp:436-438), so this
+    is a tolerance check: the reference's abs 1e-4 (stencil.cpp:137) and north_star's max
+    relative error 1e-5 for fp32, exact zeros required to agree."""
+    m, N, r, T = key.split("_")
+    N, r, T = int(N[1:]), int(r[1:]), int(T[1:])
+    a, b = _oracle_pair((N, N), r, np.float32, 0)
+    got, _ = sweep.run_host((N, N), a, b, T, radius=r)
+    g = oracle.interior(got, r).astype(np.float64)
+    gold = GOLD_EMU[key].astype(np.float64)
+    assert np.abs(g - gold).max() < 1e-4
+    assert np.array_equal(g == 0, gold == 0)
+    mx = np.maximum(np.abs(g), np.abs(gold))
+    assert (np.abs(g - gold)[mx > 0] / mx[mx > 0]).max() <= 1e-5
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
 @pytest.mark.parametrize("n,r,T", [

@@ -153,3 +153,72 @@ def test_slab_fill_and_checksum_compose():
         assert np.array_equal(slab, whole[off:off + 4 + 2 * r])
         acc = (acc + oracle.checksum((6, 5, 4), r, slab, z_offset=off, z_total=8)) % 2 ** 64
     assert acc == total
+
+
+# ---- the reference's ACCELERATOR kernels (DMA / DMASlavePack / RMA) on the athread emulator ----
+# tests/golden/ref_emu_2d_f32.npz: grids produced by the unmodified src/stencil/slave/*.cpp
+# kernels through Stencil::run on 64 emulated CPEs (oracle/ref_shim/emu/).  Their add order
+# (0.25f*(up+left+right+down), stencil_dma.cpp:436-438; row sum + column sum - 2*centre for
+# r > 1, :636-651) is not the naive loop's, so the reference's own kernels agree with its own
+# check only within its tolerance (abs 1e-4, stencil.cpp:137) — measured: <= 2 ulp of 0.5.
+GOLD_EMU = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_emu_2d_f32.npz"))
+REF_ABS_TOL = 1e-4   # stencil.cpp:137
+NORTH_STAR_REL_F32 = 1e-5
+
+
+def _emu_case(key):
+    m, n, r, t = key.split("_")
+    return m, int(n[1:]), int(r[1:]), int(t[1:])
+
+
+def rel_err(a, b):
+    """max |a-b| / max(|a|,|b|) with exact zeros required to agree."""
+    a = a.astype(np.float64)
+    b = b.astype(np.float64)
+    assert np.array_equal(a == 0, b == 0)
+    m = np.maximum(np.abs(a), np.abs(b))
+    return float((np.abs(a - b)[m > 0] / m[m > 0]).max()) if (m > 0).any() else 0.0
+
+
+@pytest.mark.parametrize("key", sorted(GOLD_EMU.files))
+def test_oracle_vs_reference_accelerator_kernels(key):
+    m, N, r, T = _emu_case(key)
+    got = oracle.interior(oracle.run((N, N), r, oracle.STAR, T), r)
+    gold = GOLD_EMU[key]
+    assert np.abs(got.astype(np.float64) - gold).max() < REF_ABS_TOL
+    assert np.abs(got.astype(np.float64) - gold).max() <= 4 * 2.0 ** -24  # measured: 2 ulp of 0.5
+    assert rel_err(got, gold) <= NORTH_STAR_REL_F32
+
+
+needs_emu = pytest.mark.skipif(oracle.ref_emu_lib() is None,
+                               reason="oracle/_ref/libref_emu.so needs /root/reference")
+
+
+@needs_emu
+@pytest.mark.parametrize("key", sorted(GOLD_EMU.files))
+def test_emulated_reference_kernels_reproduce_golden(key):
+    """Determinism of the emulation (64 threads, barriers, RMA reply counters) and the
+    reference's own verdict on its kernels."""
+    m, N, r, T = _emu_case(key)
+    g, ok = oracle.ref_emu_run_2d_f32(m, N, N // 8, r, T)
+    assert ok
+    assert np.array_equal(g.view(np.uint32), GOLD_EMU[key].view(np.uint32))
+
+
+@needs_emu
+def test_emulated_transports_agree_bitwise():
+    """DMA, DMASlavePack and RMA only differ in how halos travel: same bits."""
+    a, _ = oracle.ref_emu_run_2d_f32("DMA", 128, 16, 1, 77)
+    b, _ = oracle.ref_emu_run_2d_f32("DMASlavePack", 128, 16, 1, 77)
+    c, _ = oracle.ref_emu_run_2d_f32("RMA", 128, 16, 1, 77)
+    assert np.array_equal(a, b) and np.array_equal(a, c)
+
+
+@needs_emu
+def test_emulator_rejects_what_the_kernels_cannot_run():
+    with pytest.raises(ValueError):
+        oracle.ref_emu_run_2d_f32("RMA", 64, 8, 2, 3)       # radius 1 only
+    with pytest.raises(ValueError):
+        oracle.ref_emu_run_2d_f32("DMA", 60, 8, 1, 3)       # N must be 8 * block
+    with pytest.raises(ValueError):
+        oracle.ref_emu_run_2d_f32("DMAStaticUnroll", 64, 8, 1, 3)
