@@ -774,12 +774,11 @@ static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, 
 // right edge of parallelogram i at time level t stays in the ping-pong buffer of that parity
 // (later blocks of i write strictly below it, because block sizes never decrease), which is
 // exactly the halo parallelogram i+1 needs: no extra storage, same kernels, same bits.
-static int run_host_pipelined_impl(const sb200_desc* desc, const Choice& c, void* in, void* out,
-                                   sb200_timing* timing, int C) {
+static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
+                              sb200_timing* timing, int C) {
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t es = esize(desc->dtype);
-    const size_t bytes = (size_t)g.elems() * es;
     const long long n = outer_n(g), r = g.r, T = desc->iterations;
     const long long hx = g.n[0] + 2 * r;
     const long long rows_per_outer = g.ndim == 3 ? g.pitch_y : 1;
@@ -907,15 +906,6 @@ static int run_host_pipelined_impl(const sb200_desc* desc, const Choice& c, void
     return SB200_OK;
 }
 
-static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
-                              sb200_timing* timing, int C) {
-    const int rc = run_host_pipelined_impl(desc, c, in, out, timing, C);
-    // an error return may leave copies and launches in flight on the internal streams that
-    // still use the caller's host buffers: drain them before handing control back
-    if (rc != SB200_OK) cudaDeviceSynchronize();
-    return rc;
-}
-
 int sb200_upload(const sb200_desc* desc, uint32_t ghost, const void* host, void* dev, void* stream) {
     if (int rc = validate(desc)) return rc;
     if (!host || !dev) return fail(SB200_ERR_INVALID, "null buffer");
@@ -986,11 +976,20 @@ int sb200_host_unregister(void* ptr) {
     return SB200_OK;
 }
 
+static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timing* timing);
+
 int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* timing) {
     if (int rc = validate(desc)) return rc;
     if (!in || !out) return fail(SB200_ERR_INVALID, "null host buffer");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
+    const int rc = run_host_impl(desc, in, out, timing);
+    // an error return may leave a copy from / to the caller's host buffers in flight
+    if (rc != SB200_OK) cudaDeviceSynchronize();
+    return rc;
+}
+
+static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timing* timing) {
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t bytes = (size_t)g.elems() * esize(desc->dtype);
