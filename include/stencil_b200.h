@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define SB200_ABI_VERSION 2 /* 2: slab link, resident2d, plan, host_register */
+#define SB200_ABI_VERSION 3 /* 2: slab link, resident2d, plan, host_register; 3: pipeline_schedule */
 
 typedef enum sb200_status {
     SB200_OK = 0,
@@ -233,6 +233,32 @@ typedef struct sb200_plan_info {
     uint32_t pipeline_chunks; /* (z,t) parallelograms of sb200_run_host; 1 = not pipelined */
 } sb200_plan_info;
 int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_info* info);
+
+/* The schedule sb200_run_host executes for a grid it pipelines (plan.pipeline_chunks > 1), as
+ * plain data — pure host logic, no device needed.  Ops of one stream run in issue order (the
+ * order of the list); `wait` adds cross-stream happens-before edges.  The device holds a dense
+ * staging image of `in` plus two ping-pong grids (0, 1).  *count = 0 for a call that is not
+ * pipelined.  With capacity = 0 only the op count is returned. */
+typedef enum sb200_pipe_kind {
+    SB200_PIPE_UPLOAD = 0,   /* host `in` -> staging, padded outermost indices [lo, hi)            */
+    SB200_PIPE_UNPACK = 1,   /* staging -> grids 0 AND 1 (re-pitch), padded outermost [lo, hi)     */
+    SB200_PIPE_SWEEP = 2,    /* `steps` fused steps grid src -> grid 1-src, interior outermost
+                                output indices [lo, hi); reads [lo - steps*r, hi + steps*r) of src,
+                                clipped to the grid incl. its Dirichlet halo                        */
+    SB200_PIPE_DOWNLOAD = 3  /* grid src, interior outermost [lo, hi) -> the host result buffer     */
+} sb200_pipe_kind;
+typedef struct sb200_pipe_op {
+    int32_t kind;          /* sb200_pipe_kind */
+    int32_t stream;        /* 0 = copy-in, 1 = copy-out, 2.. = sweep streams */
+    int32_t parallelogram; /* which (z,t) parallelogram the op belongs to */
+    int32_t block;         /* SWEEP: index of the fused block, else -1 */
+    uint32_t steps;        /* SWEEP: fused steps */
+    int32_t src;           /* SWEEP / DOWNLOAD: ping-pong grid read */
+    int64_t lo, hi;
+    int32_t wait[2];       /* indices of ops that must complete first; -1 = none */
+} sb200_pipe_op;
+int sb200_pipeline_schedule(const sb200_desc* desc, sb200_pipe_op* ops, uint32_t capacity,
+                            uint32_t* count);
 
 /* Largest time block the chosen kernel family supports for this descriptor. */
 int sb200_max_time_block(const sb200_desc* desc);

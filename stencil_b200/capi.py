@@ -26,8 +26,9 @@ SYMBOLS = [
     "sb200_checksum_device", "sb200_host_alloc", "sb200_host_free", "sb200_max_time_block",
     "sb200_device_alloc", "sb200_device_free", "sb200_ipc_export", "sb200_ipc_open",
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
-    "sb200_host_register", "sb200_host_unregister", "sb200_plan",
+    "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
 ]
+PIPE_UPLOAD, PIPE_UNPACK, PIPE_SWEEP, PIPE_DOWNLOAD = 0, 1, 2, 3
 IPC_HANDLE_BYTES = 64
 LINK_FLAG_WORDS = 4
 
@@ -74,6 +75,14 @@ class PlanInfo(ctypes.Structure):
     ]
 
 
+class PipeOp(ctypes.Structure):
+    _fields_ = [
+        ("kind", ctypes.c_int32), ("stream", ctypes.c_int32), ("parallelogram", ctypes.c_int32),
+        ("block", ctypes.c_int32), ("steps", ctypes.c_uint32), ("src", ctypes.c_int32),
+        ("lo", ctypes.c_int64), ("hi", ctypes.c_int64), ("wait", ctypes.c_int32 * 2),
+    ]
+
+
 class StencilError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"stencil_b200 error {code}: {msg}")
@@ -115,6 +124,7 @@ def lib() -> ctypes.CDLL:
         L.sb200_host_unregister.argtypes = [vp]
         L.sb200_plan.argtypes = [dp, u32, i32, ctypes.POINTER(PlanInfo)]
         L.sb200_max_time_block.argtypes = [dp]
+        L.sb200_pipeline_schedule.argtypes = [dp, ctypes.POINTER(PipeOp), u32, ctypes.POINTER(u32)]
         L.sb200_device_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_device_free.argtypes = [vp]
         L.sb200_ipc_export.argtypes = [vp, ctypes.c_char_p]
@@ -150,6 +160,18 @@ def layout_for(desc: Desc, ghost: int = 0) -> Layout:
     lay = Layout()
     check(lib().sb200_layout_for(ctypes.byref(desc), ghost, ctypes.byref(lay)))
     return lay
+
+
+def pipeline_schedule(desc: Desc) -> list:
+    """The op list sb200_run_host would execute for this descriptor ([] if it does not
+    pipeline the call); host logic only."""
+    n = ctypes.c_uint32(0)
+    check(lib().sb200_pipeline_schedule(ctypes.byref(desc), None, 0, ctypes.byref(n)))
+    if n.value == 0:
+        return []
+    ops = (PipeOp * n.value)()
+    check(lib().sb200_pipeline_schedule(ctypes.byref(desc), ops, n.value, ctypes.byref(n)))
+    return list(ops)
 
 
 def plan(desc: Desc, steps: int, sm_count: int = 148) -> PlanInfo:

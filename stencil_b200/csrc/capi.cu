@@ -770,16 +770,90 @@ static int pipeline_chunks(const sb200_desc* d, const Choice& c, const Grid& g, 
 // Parallelogram i only needs the planes below its right edge, so it starts as soon as upload
 // chunk i has landed, and its final region [F_i, F_i+1) is complete — and starts its way
 // back to the host — while the parallelograms to its right are still being swept.  H2D, the
-// sweep and D2H run on three streams; PCIe is used in both directions at once.  The slanted
+// sweep and D2H run on separate streams; PCIe is used in both directions at once.  The slanted
 // right edge of parallelogram i at time level t stays in the ping-pong buffer of that parity
 // (later blocks of i write strictly below it, because block sizes never decrease), which is
 // exactly the halo parallelogram i+1 needs: no extra storage, same kernels, same bits.
+//
+// The schedule is built first, as plain data (sb200_pipe_op: what, on which stream, over which
+// planes, after which other ops), and executed afterwards: the same list is handed out by
+// sb200_pipeline_schedule so that its geometry and its happens-before edges can be checked on a
+// CPU (tests/test_pipeline_schedule.py proves every pair of unordered ops conflict-free).
+static int pipeline_streams() {
+    int NS = 2;
+    if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) < 1 ? 1 : (atoi(e) > 4 ? 4 : atoi(e));
+    return NS;
+}
+
+static void build_pipeline(const sb200_desc* desc, const Choice& c, const Grid& g, int C, int NS,
+                           std::vector<sb200_pipe_op>& ops) {
+    const long long n = outer_n(g), r = g.r, T = desc->iterations;
+    const long long n_outer_padded = g.ndim == 3 ? g.planes : g.pitch_y;
+    // Starting edges Z_i: C-1 equal upload chunks, then a last parallelogram that starts with
+    // zero width at the high end (a triangle growing to T*r planes).  Final regions
+    // F_i = Z_i - T*r clipped at 0: parallelograms that drift out of the grid before step T
+    // (the first ~T*r planes) download nothing, so the first upload chunk does not have to
+    // cover the whole drift before sweeping starts.
+    std::vector<long long> F(C + 1), Z(C + 1);
+    for (int i = 0; i < C; ++i) {
+        Z[i] = n * i / (C - 1);
+        F[i] = Z[i] - T * r > 0 ? Z[i] - T * r : 0;
+    }
+    Z[C] = F[C] = n;
+    // block sizes: the short remainder block FIRST, so block sizes never decrease
+    std::vector<int> blocks;
+    if (T % c.k) blocks.push_back((int)(T % c.k));
+    for (long long b = 0; b < T / c.k; ++b) blocks.push_back(c.k);
+    const size_t nb = blocks.size();
+    auto add = [&](int kind, int stream, int par, int block, uint32_t steps, int src, long long lo, long long hi,
+                   int w0) {
+        sb200_pipe_op o;
+        o.kind = kind; o.stream = stream; o.parallelogram = par; o.block = block; o.steps = steps; o.src = src;
+        o.lo = lo; o.hi = hi; o.wait[0] = w0; o.wait[1] = -1;
+        ops.push_back(o);
+        return (int)ops.size() - 1;
+    };
+    ops.clear();
+    // upload chunk i = padded outer indices [U_i, U_i+1), all on the copy-in stream
+    std::vector<int> up(C);
+    for (int i = 0; i < C; ++i) {
+        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
+        up[i] = add(SB200_PIPE_UPLOAD, 0, i, -1, 0, -1, ub, ue, -1);
+    }
+    // Consecutive parallelograms alternate between the sweep streams and run as a wavefront:
+    // block b of parallelogram i+1 only waits for block b-1 of parallelogram i (its slanted
+    // left halo; the same edge orders the write-after-read on the ping-pong buffer), so the
+    // thin range launches of neighbouring parallelograms fill each other's partial waves.
+    // last_before[b] = the newest op of the previous parallelogram issued up to its block b-1
+    // (an empty block launches nothing; the op before it on that stream stands in for it).
+    std::vector<int> prev_upto(nb + 1, -1), cur_upto(nb + 1, -1);
+    for (int i = 0; i < C; ++i) {
+        const int ss = 2 + i % NS;
+        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
+        int last = add(SB200_PIPE_UNPACK, ss, i, -1, 0, -1, ub, ue, up[i]);
+        cur_upto[0] = last;  // what "block -1" of this parallelogram means to its right neighbour
+        long long done_steps = 0;
+        for (size_t b = 0; b < nb; ++b) {
+            done_steps += blocks[b];
+            long long L = i == 0 ? 0 : Z[i] - done_steps * r;
+            long long R = i == C - 1 ? n : Z[i + 1] - done_steps * r;
+            if (L < 0) L = 0;
+            if (R > n) R = n;
+            if (R > L) last = add(SB200_PIPE_SWEEP, ss, i, (int)b, (uint32_t)blocks[b], (int)(b & 1), L, R,
+                                  i > 0 ? prev_upto[b] : -1);
+            cur_upto[b + 1] = last;
+        }
+        if (F[i + 1] > F[i]) add(SB200_PIPE_DOWNLOAD, 1, i, -1, 0, (int)(nb & 1), F[i], F[i + 1], last);
+        prev_upto.swap(cur_upto);
+    }
+}
+
 static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
                               sb200_timing* timing, int C) {
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t es = esize(desc->dtype);
-    const long long n = outer_n(g), r = g.r, T = desc->iterations;
+    const long long r = g.r;
     const long long hx = g.n[0] + 2 * r;
     const long long rows_per_outer = g.ndim == 3 ? g.pitch_y : 1;
     const long long n_outer_padded = g.ndim == 3 ? g.planes : g.pitch_y;
@@ -797,94 +871,67 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         CU_TRY(cudaStreamCreateWithFlags(&S.st_out, cudaStreamNonBlocking));
         for (auto& q : S.st_sweep) CU_TRY(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
     }
+    const int NS = pipeline_streams();
+    std::vector<sb200_pipe_op> ops;
+    build_pipeline(desc, c, g, C, NS, ops);
     cudaStream_t st = 0;  // the caller's stream: start / end of the whole pipeline
-    // Starting edges Z_i: C-1 equal upload chunks, then a last parallelogram that starts with
-    // zero width at the high end (a triangle growing to T*r planes).  Final regions
-    // F_i = Z_i - T*r clipped at 0: parallelograms that drift out of the grid before step T
-    // (the first ~T*r planes) download nothing, so the first upload chunk does not have to
-    // cover the whole drift before sweeping starts.
-    std::vector<long long> F(C + 1), Z(C + 1);
-    for (int i = 0; i < C; ++i) {
-        Z[i] = n * i / (C - 1);
-        F[i] = Z[i] - T * r > 0 ? Z[i] - T * r : 0;
-    }
-    Z[C] = F[C] = n;
+    auto stream_of = [&](const sb200_pipe_op& o) { return o.stream == 0 ? S.st_in : o.stream == 1 ? S.st_out : S.st_sweep[o.stream - 2]; };
+    // one event per op that another op waits for
     Events events;
-    std::vector<cudaEvent_t> up(C), done(C);
     cudaEvent_t ev[4];
     for (auto& e : ev) e = events.make(cudaEventDefault);
-    for (int i = 0; i < C; ++i) {
-        up[i] = events.make();
-        done[i] = events.make();
-    }
+    std::vector<cudaEvent_t> op_done(ops.size(), nullptr);
+    for (const auto& o : ops)
+        for (int w : o.wait)
+            if (w >= 0 && !op_done[(size_t)w]) op_done[(size_t)w] = events.make();
     CU_TRY(events.err);
     CU_TRY(cudaEventRecord(ev[0], st));
     CU_TRY(cudaStreamWaitEvent(S.st_in, ev[0], 0));
-    // upload chunk i = padded outer indices [U_i, U_i+1)
-    for (int i = 0; i < C; ++i) {
-        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
-        CU_TRY(cudaMemcpyAsync((char*)S.staging + ub * outer_bytes, (const char*)in + ub * outer_bytes,
-                               (size_t)(ue - ub) * outer_bytes, cudaMemcpyHostToDevice, S.st_in));
-        CU_TRY(cudaEventRecord(up[i], S.st_in));
-    }
-    CU_TRY(cudaEventRecord(ev[1], S.st_in));
-    // block sizes: the short remainder block FIRST, so block sizes never decrease
-    std::vector<int> blocks;
-    if (T % c.k) blocks.push_back((int)(T % c.k));
-    for (long long b = 0; b < T / c.k; ++b) blocks.push_back(c.k);
+    CU_TRY(cudaStreamWaitEvent(S.st_out, ev[0], 0));
+    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
     const Domain dom = make_domain(g, 1, 1);
     void* buf[2] = {S.buf[0], S.buf[1]};
+    void* host_dst = (desc->iterations & 1u) ? out : in;
     uint32_t nl = 0;
-    // Consecutive parallelograms alternate between two sweep streams and run as a wavefront:
-    // block b of parallelogram i+1 only waits for block b-1 of parallelogram i (its slanted
-    // left halo; the same edge orders the write-after-read on the ping-pong buffer), so the
-    // thin range launches of neighbouring parallelograms fill each other's partial waves.
-    int NS = 2;
-    if (const char* e = getenv("SB200_PIPELINE_STREAMS")) NS = atoi(e) < 1 ? 1 : (atoi(e) > 4 ? 4 : atoi(e));
-    const size_t nb = blocks.size();
-    std::vector<cudaEvent_t> unpacked(C), bd((size_t)C * nb);
-    for (auto& e : unpacked) e = events.make();
-    for (auto& e : bd) e = events.make();
-    CU_TRY(events.err);
-    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
+    int uploads_left = 0;
+    for (const auto& o : ops) uploads_left += o.kind == SB200_PIPE_UPLOAD;
     bool first_download = false;
-    for (int i = 0; i < C; ++i) {
-        cudaStream_t ss = S.st_sweep[i % NS];
-        const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
-        CU_TRY(cudaStreamWaitEvent(ss, up[i], 0));
-        {
-            const long long rb = ub * rows_per_outer, re = ue * rows_per_outer;
-            dim3 grid((unsigned)((g.pitch_x + 255) / 256), (unsigned)((re - rb) < 65535 ? (re - rb) : 65535));
-            if (desc->dtype == SB200_F64)
-                unpack_dense2_kernel<double><<<grid, 256, 0, ss>>>((const double*)S.staging, (double*)buf[0], (double*)buf[1], g, hx, rb, re);
-            else
-                unpack_dense2_kernel<float><<<grid, 256, 0, ss>>>((const float*)S.staging, (float*)buf[0], (float*)buf[1], g, hx, rb, re);
-            CU_TRY(cudaGetLastError());
-        }
-        CU_TRY(cudaEventRecord(unpacked[i], ss));
-        long long done_steps = 0;
-        for (size_t b = 0; b < nb; ++b) {
-            done_steps += blocks[b];
-            long long L = i == 0 ? 0 : Z[i] - done_steps * r;
-            long long R = i == C - 1 ? n : Z[i + 1] - done_steps * r;
-            if (L < 0) L = 0;
-            if (R > n) R = n;
-            if (i > 0) CU_TRY(cudaStreamWaitEvent(ss, b == 0 ? unpacked[i - 1] : bd[(size_t)(i - 1) * nb + b - 1], 0));
-            if (R > L) {
-                if (int rc = pass(desc, c, g, dom, buf[b & 1], buf[(b + 1) & 1], blocks[b], L, R, ss)) return rc;
-                ++nl;
+    for (size_t j = 0; j < ops.size(); ++j) {
+        const sb200_pipe_op& o = ops[j];
+        cudaStream_t ss = stream_of(o);
+        for (int w : o.wait)
+            if (w >= 0) CU_TRY(cudaStreamWaitEvent(ss, op_done[(size_t)w], 0));
+        switch (o.kind) {
+            case SB200_PIPE_UPLOAD:
+                CU_TRY(cudaMemcpyAsync((char*)S.staging + o.lo * outer_bytes, (const char*)in + o.lo * outer_bytes,
+                                       (size_t)(o.hi - o.lo) * outer_bytes, cudaMemcpyHostToDevice, ss));
+                if (--uploads_left == 0) CU_TRY(cudaEventRecord(ev[1], ss));
+                break;
+            case SB200_PIPE_UNPACK: {
+                const long long rb = o.lo * rows_per_outer, re = o.hi * rows_per_outer;
+                dim3 grid((unsigned)((g.pitch_x + 255) / 256), (unsigned)((re - rb) < 65535 ? (re - rb) : 65535));
+                if (desc->dtype == SB200_F64)
+                    unpack_dense2_kernel<double><<<grid, 256, 0, ss>>>((const double*)S.staging, (double*)buf[0], (double*)buf[1], g, hx, rb, re);
+                else
+                    unpack_dense2_kernel<float><<<grid, 256, 0, ss>>>((const float*)S.staging, (float*)buf[0], (float*)buf[1], g, hx, rb, re);
+                CU_TRY(cudaGetLastError());
+                break;
             }
-            if (i + 1 < C) CU_TRY(cudaEventRecord(bd[(size_t)i * nb + b], ss));
+            case SB200_PIPE_SWEEP:
+                if (int rc = pass(desc, c, g, dom, buf[o.src], buf[o.src ^ 1], (int)o.steps, o.lo, o.hi, ss)) return rc;
+                ++nl;
+                break;
+            case SB200_PIPE_DOWNLOAD:
+                if (!first_download) {
+                    CU_TRY(cudaEventRecord(ev[2], ss));
+                    first_download = true;
+                }
+                if (int rc = download_interior_range(desc, buf[o.src], host_dst, o.lo, o.hi, ss)) return rc;
+                break;
         }
-        CU_TRY(cudaEventRecord(done[i], ss));
-        CU_TRY(cudaStreamWaitEvent(S.st_out, done[i], 0));
-        if (!first_download && (F[i + 1] > F[i] || i == C - 1)) {
-            CU_TRY(cudaEventRecord(ev[2], S.st_out));
-            first_download = true;
-        }
-        void* host_dst = (desc->iterations & 1u) ? out : in;
-        if (int rc = download_interior_range(desc, buf[nb & 1], host_dst, F[i], F[i + 1], S.st_out)) return rc;
+        if (op_done[j]) CU_TRY(cudaEventRecord(op_done[j], ss));
     }
+    if (!first_download) CU_TRY(cudaEventRecord(ev[2], S.st_out));
     CU_TRY(cudaEventRecord(ev[3], S.st_out));
     CU_TRY(cudaStreamWaitEvent(st, ev[3], 0));
     CU_TRY(cudaStreamSynchronize(S.st_out));
@@ -903,6 +950,24 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         timing->kernel = c.kernel;
         timing->result_in_out = (int)(desc->iterations & 1u);
     }
+    return SB200_OK;
+}
+
+int sb200_pipeline_schedule(const sb200_desc* desc, sb200_pipe_op* ops_out, uint32_t capacity, uint32_t* count) {
+    if (int rc = validate(desc)) return rc;
+    if (!count || (capacity && !ops_out)) return fail(SB200_ERR_INVALID, "bad argument");
+    const Choice c = choose(desc);
+    if (int rc = check_choice(desc, c)) return rc;
+    const Grid g = make_grid(desc, 0);
+    const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * esize(desc->dtype);
+    const int C = pipeline_chunks(desc, c, g, dense);
+    *count = 0;
+    if (C <= 1) return SB200_OK;  // not pipelined: upload, sweep, download back to back
+    std::vector<sb200_pipe_op> ops;
+    build_pipeline(desc, c, g, C, pipeline_streams(), ops);
+    *count = (uint32_t)ops.size();
+    if (ops.size() > capacity) return capacity ? fail(SB200_ERR_INVALID, "schedule has %zu ops, capacity %u", ops.size(), capacity) : SB200_OK;
+    memcpy(ops_out, ops.data(), ops.size() * sizeof(sb200_pipe_op));
     return SB200_OK;
 }
 

@@ -20,7 +20,7 @@ def test_header_symbols_all_exported(built):
     L = capi.lib()
     for s in declared:
         assert getattr(L, s) is not None
-    assert L.sb200_abi_version() == 2
+    assert L.sb200_abi_version() == 3
 
 
 def test_struct_sizes_match_header(built):
