@@ -201,6 +201,9 @@ def ref_emu_run_2d_f32(method: str, N: int, block: int, r: int, T: int):
         raise RuntimeError("oracle/_ref/libref_emu.so not built (needs /root/reference)")
     out = np.empty((N, N), dtype=np.float32)
     ok = ctypes.c_int(-1)
-    if R.ref_emu_run_2d_f32(method.encode(), N, block, r, T, out.ctypes.data, ctypes.byref(ok)) != 0:
+    rc = R.ref_emu_run_2d_f32(method.encode(), N, block, r, T, out.ctypes.data, ctypes.byref(ok))
+    if rc == -2:
+        raise RuntimeError("athread emulator: the emulated CPE stacks are not congruent on this host")
+    if rc != 0:
         raise ValueError(f"emulated reference kernel cannot run {method} N={N} block={block} r={r} T={T}")
     return out, bool(ok.value)

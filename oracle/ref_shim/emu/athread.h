@@ -26,6 +26,7 @@ typedef volatile int athread_rply_t;
 int athread_init(void);
 int athread_spawn(void* fn, void* arg);
 int athread_join(void);
+int sb200_emu_last_spawn_failed(void); /* emulator only: the CPE stacks were not congruent */
 
 /* ---- CPE side ---- */
 extern __thread int sb200_emu_row, sb200_emu_col;

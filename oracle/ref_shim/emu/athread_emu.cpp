@@ -24,6 +24,7 @@ bool g_running = false;
 void (*g_fn)(void*) = nullptr;
 void* g_arg = nullptr;
 ptrdiff_t g_marker_off[kCpes];
+bool g_failed = false;  // the CPE stacks were not congruent: the kernel was not run
 
 __thread int t_id = -1;
 __thread size_t t_heap_top = 0;
@@ -64,10 +65,13 @@ void* trampoline(void* idp) {
     sb200_emu_col = t_id % kMesh;
     g_marker_off[t_id] = const_cast<char*>(&marker) - arena(t_id);
     pthread_barrier_wait(&g_barrier);
-    // identical stack layout in every CPE is what makes stack addresses translatable
-    if (g_marker_off[t_id] != g_marker_off[0]) {
-        std::fprintf(stderr, "athread emulator: CPE stacks are not congruent\n");
-        std::abort();
+    // identical stack layout in every CPE is what makes stack addresses translatable; every
+    // CPE takes the same decision, so nobody is left waiting at a barrier
+    bool congruent = true;
+    for (int i = 1; i < kCpes; ++i) congruent = congruent && g_marker_off[i] == g_marker_off[0];
+    if (!congruent) {
+        g_failed = true;
+        return nullptr;
     }
     g_fn(g_arg);
     return nullptr;
@@ -78,6 +82,10 @@ extern "C" {
 __thread int sb200_emu_row = 0, sb200_emu_col = 0;
 
 int athread_init(void) { return 0; }
+// 1 if the last spawn could not run its kernel (reported by athread_join as -2 too); the
+// reference's Stencil::run ignores athread_join's result, so the driver asks here
+static bool g_last_failed = false;
+int sb200_emu_last_spawn_failed(void) { return g_last_failed ? 1 : 0; }
 
 int athread_spawn(void* fn, void* arg) {
     if (g_running) return -1;
@@ -109,6 +117,11 @@ int athread_join(void) {
     for (int i = 0; i < kCpes; ++i) pthread_join(g_threads[i], nullptr);
     pthread_barrier_destroy(&g_barrier);
     g_running = false;
+    g_last_failed = g_failed;
+    if (g_failed) {
+        g_failed = false;
+        return -2;
+    }
     return 0;
 }
 

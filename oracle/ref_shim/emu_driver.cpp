@@ -29,7 +29,7 @@ void slave_stencil_iterate_dma_static_unroll(Arguments*) {}
 // method: "DMA" | "DMASlavePack" | "RMA".  N must be 8 * block (every CPE owns one block and
 // takes part in every barrier).  out[N*N] receives the interior after T iterations;
 // *self_check = the reference's own check_result() verdict (1 = within 1e-4 of its naive loop).
-// Returns 0, -1 for a bad request.
+// Returns 0, -1 for a bad request, -2 if the emulator could not run the kernel.
 int ref_emu_run_2d_f32(const char* method, unsigned N, unsigned block, unsigned r, unsigned T, float* out,
                        int* self_check) {
     const std::string m(method ? method : "");
@@ -47,6 +47,7 @@ int ref_emu_run_2d_f32(const char* method, unsigned N, unsigned block, unsigned 
     Stencil s(opts);
     athread_init();
     s.run(std::string_view(m));
+    if (sb200_emu_last_spawn_failed()) return -2;  // the emulator could not set up the CPE array
     auto& fin = (T & 1u) ? s.result : s.matrix;  // stencil.cpp:88-92,129-134
     for (unsigned row = 0; row != N; ++row)
         for (unsigned col = 0; col != N; ++col) out[(size_t)row * N + col] = fin.elem_at(row, col);
