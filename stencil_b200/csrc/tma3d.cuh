@@ -23,6 +23,7 @@
 #include <array>
 #include <functional>
 #include <map>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -47,6 +48,15 @@ template <class T, int K> struct T3 {
     static constexpr size_t SMEM =
         PLANE_BYTES * STAGES + (size_t)EDGE * sizeof(T) * 2 * (K - 1) + 8 * STAGES + 128;
 };
+// tools/sm_bound_probe.sh builds a second library with -DSB200_PROBE_ZWRAP=8: every CTA then
+// streams the same 8 planes over and over (loads and stores stay in L2, results are garbage),
+// which measures the SM-side rate of the kernel without the HBM limit.  Never defined in
+// the product build.
+#ifdef SB200_PROBE_ZWRAP
+#define T3_PROBE_Z(j) ((j) & (SB200_PROBE_ZWRAP - 1))
+#else
+#define T3_PROBE_Z(j) (j)
+#endif
 constexpr int T3_MAXK = 3;      // star
 constexpr int T3_MAXK_BOX = 2;  // box (27-point)
 
@@ -311,7 +321,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
     if (tid == 0) {
         for (int s = 0; s < S && s < nin; ++s) {
             mbar_expect_tx(&bars[s], (uint32_t)C::PLANE_BYTES);
-            tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, cz0 + s);
+            tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, cz0 + T3_PROBE_Z(s));
         }
     }
 
@@ -369,7 +379,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
     const long long plane_stride = g.pitch_x * g.pitch_y;
     const long long row_stride = g.pitch_x;
     // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
-    T* __restrict__ outp = out + g.idx(gx, gy, z_first - 2 * K + 1);
+    T* __restrict__ outp_run = out + g.idx(gx, gy, z_first - 2 * K + 1);
     // One time level of one plane step.  L = level index (level L+1 of the fused block),
     // P = j & 1.  Level L consumes the plane its lower level emitted on the PREVIOUS step
     // (registers + the edge rows published in shared memory), so one barrier per step
@@ -425,6 +435,11 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
                         if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
             }
             if (pe >= p_out_lo && pe < p_out_hi) {
+#ifdef SB200_PROBE_ZWRAP
+                T* __restrict__ outp = outp_run - (long long)((pe - K) & ~(SB200_PROBE_ZWRAP - 1)) * plane_stride;
+#else
+                T* __restrict__ outp = outp_run;
+#endif
                 if (store_fast) {
 #pragma unroll
                     for (int i = 0; i < PY; ++i) VecN<T, PXV>::st(outp + i * row_stride, o[i]);
@@ -450,12 +465,12 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
         if constexpr (K > 2) level(IC<2>{}, Pc, j);
         if constexpr (K > 1) level(IC<1>{}, Pc, j);
         level(IC<0>{}, Pc, j);
-        outp += plane_stride;
+        outp_run += plane_stride;
         __syncthreads();
         if (tid == 0 && j + S < nin) {
             const int st = j & (S - 1);
             mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
-            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + j + S);
+            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + T3_PROBE_Z(j + S));
         }
     };
     // steps past nsteps (loop rounded up to the phase count) wait for nothing and store nothing
@@ -520,7 +535,10 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
     p.ntx = (int)((nx + C::VX - 1) / C::VX);
     p.nty = (int)((ny + C::VY - 1) / C::VY);
     const long long tiles = (long long)p.ntx * p.nty;
+    // one cache per instantiation, shared by every host thread (slab workers, planners)
     static std::map<std::array<long long, 6>, std::pair<int, long long>> cache;
+    static std::mutex cache_mu;
+    std::lock_guard<std::mutex> cache_lock(cache_mu);
     const std::array<long long, 6> key = {nx, ny, planes, sm_count, K, (long long)sizeof(T)};
     auto it = cache.find(key);
     if (it == cache.end()) {
