@@ -23,7 +23,8 @@
 extern "C" {
 #endif
 
-#define SB200_ABI_VERSION 3 /* 2: slab link, resident2d, plan, host_register; 3: pipeline_schedule */
+#define SB200_ABI_VERSION 4 /* 2: slab link, resident2d, plan, host_register; 3: pipeline_schedule;
+                               4: ngpus/flags in sb200_desc, sb200_init_multi, slab plans, prepare */
 
 typedef enum sb200_status {
     SB200_OK = 0,
@@ -64,9 +65,22 @@ typedef struct sb200_desc {
     uint64_t n[3];       /* interior extents x,y,z */
     uint32_t iterations; /* T */
     uint32_t time_block; /* fused steps per HBM round trip; 0 = auto */
-    uint32_t block_hint; /* reference -b/--block-size; a tuning hint only */
+    uint32_t block_hint; /* reference -b/--block-size (program_options.cpp:16-18): the CUDA
+                            backend reads it as a tile / time-block preference, see sb200_plan */
     int32_t kernel;      /* sb200_kernel */
+    uint32_t ngpus;      /* sb200_run_host: GPUs of this process to spread the grid over, as
+                            z-slabs (y-slabs in 2-D); 0 = every device bound by sb200_init /
+                            sb200_init_multi.  Ignored by the device-resident calls. */
+    uint32_t flags;      /* sb200_flags */
 } sb200_desc;
+
+typedef enum sb200_flags {
+    SB200_FLAG_NONE = 0,
+    /* Allow kernels that re-associate the sum of a point (separable box sums): results
+     * then agree with the reference order within the north-star tolerance (max relative
+     * error 1e-12 fp64 / 1e-5 fp32) instead of bit for bit.  Off by default. */
+    SB200_FLAG_REASSOCIATE = 1
+} sb200_flags;
 
 /* Timing breakdown of one call (milliseconds; device times from CUDA events).
  * Small grids run upload -> sweep -> download back to back and the three device
@@ -84,6 +98,8 @@ typedef struct sb200_timing {
     uint32_t time_block;   /* fused depth actually used */
     int32_t kernel;        /* family actually used */
     int32_t result_in_out; /* 1: step T is in `out`, 0: in `in` (T parity) */
+    uint32_t ngpus;        /* GPUs the call was spread over (device times: max over them) */
+    uint32_t pipelined;    /* 1: upload / sweep / download overlapped (see above) */
 } sb200_timing;
 
 /* Device-side grid layout chosen by the library for a descriptor: padded so the
@@ -103,8 +119,17 @@ int sb200_abi_version(void);
 const char* sb200_last_error(void);
 /* Number of visible CUDA devices (0 if none / driver missing). */
 int sb200_device_count(void);
-/* Bind the calling process to `device` (one process per GPU). */
+/* Bind the calling process to `device` (one process per GPU).  Takes the one-time costs
+ * (context, module load, streams) so that the first timed call does not. */
 int sb200_init(int device);
+/* Bind the calling process to `n` devices at once (one process, N GPUs): the counterpart of
+ * the reference's single Stencil::run driving the whole 64-CPE mesh from one host thread
+ * (src/stencil/stencil.cpp:34-53; run.sh:3 `-cgsp 64`).  devices == NULL means 0..n-1.
+ * sb200_run_host then spreads a grid over them (sb200_desc.ngpus); the device-resident
+ * calls keep operating on the first device of the group. */
+int sb200_init_multi(int n, const int* devices);
+/* Number of devices bound by sb200_init / sb200_init_multi (0 before). */
+int sb200_group_size(void);
 void sb200_finalize(void);
 
 /* ---- the drop-in call -------------------------------------------------------
@@ -112,8 +137,43 @@ void sb200_finalize(void);
  * Runs T = desc->iterations double-buffered sweeps on the GPU.  On return the
  * buffer selected by T's parity holds step T (odd: out, even: in), exactly like
  * the reference kernels that swap their host views every step
- * (stencil_dma.cpp:556-557; oracle stencil.cpp:129-134).  Blocking. */
+ * (stencil_dma.cpp:556-557; oracle stencil.cpp:129-134).  Blocking.
+ *
+ * Precondition (checked on a sample, SB200_ERR_INVALID if violated): `out` carries the same
+ * halo as `in` — true for the reference's generate_initialized_matrix (stencil.cpp:190-207),
+ * which builds both matrices alike.  Only `in` crosses PCIe; its halo is cloned into both
+ * device buffers and the interior of `out` is never read.
+ *
+ * With more than one device bound (sb200_init_multi) and desc->ngpus != 1 the grid is cut
+ * into slabs along the outermost axis, one per GPU, see sb200_slab_plan.  The bits do not
+ * depend on the number of GPUs. */
 int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* timing);
+
+/* Untimed preparation of sb200_run_host(desc): allocates the device grids and the staging
+ * image on every GPU the call will use and launches each kernel variant it will take once,
+ * so that a timed call right after measures the steady state (the reference does its
+ * accelerator bring-up, athread_init(), before the timed runs too: src/main.cpp:54).
+ * Optional: sb200_run_host does all of it on demand. */
+int sb200_prepare(const sb200_desc* desc);
+
+/* How sb200_run_host spreads `desc` over `ngpus` devices — pure host logic, no device needed.
+ * Slab g OWNS outermost interior indices [own_lo, own_hi) and works on the sub-grid
+ * [sub_lo, sub_hi) = its own planes plus T*radius planes of deep halo on every internal
+ * side, read straight from the caller's host array: after t steps the sub-grid is exact on
+ * [own_lo - (T-t)*radius, own_hi + (T-t)*radius), so the slabs never talk to each other and
+ * each runs the pipelined (z,t)-parallelogram schedule on its own PCIe link.  The deep halo is
+ * redundant upload and compute, so slabs thinner than 2*T*radius planes are not used:
+ * ngpus_used is the largest count <= ngpus whose slabs are thick enough (1 = single-GPU path). */
+#define SB200_MAX_GPUS 16
+typedef struct sb200_slab_plan {
+    uint32_t ngpus_used;
+    uint32_t deep_halo; /* T * radius */
+    struct {
+        uint64_t sub_lo, sub_hi; /* sub-grid, outermost interior indices of the whole grid */
+        uint64_t own_lo, own_hi; /* planes this slab downloads */
+    } slab[SB200_MAX_GPUS];
+} sb200_slab_plan;
+int sb200_slab_plan_for(const sb200_desc* desc, int ngpus, sb200_slab_plan* plan);
 
 /* ---- device-resident API (bench, multi-GPU slabs) ----------------------------
  * `ghost` = extra planes on each side of the outermost axis beyond `radius`
@@ -259,6 +319,14 @@ typedef struct sb200_pipe_op {
 } sb200_pipe_op;
 int sb200_pipeline_schedule(const sb200_desc* desc, sb200_pipe_op* ops, uint32_t capacity,
                             uint32_t* count);
+/* The schedule of slab `slab` of sb200_slab_plan_for(desc, ngpus): indices are local to the
+ * slab's sub-grid (add slab[].sub_lo for indices of the whole grid).  Differences to the
+ * single-GPU schedule: sweeps and downloads are clipped to the dependency cone of the owned
+ * planes, and the deep-halo zones (host planes another slab downloads into when T is even)
+ * are uploaded FIRST; every slab's downloads start only after its neighbours' zone uploads
+ * (`zone_uploads` = how many leading UPLOAD ops that is; a cross-device event at run time). */
+int sb200_pipeline_schedule_slab(const sb200_desc* desc, int ngpus, int slab, sb200_pipe_op* ops,
+                                 uint32_t capacity, uint32_t* count, uint32_t* zone_uploads);
 
 /* Largest time block the chosen kernel family supports for this descriptor. */
 int sb200_max_time_block(const sb200_desc* desc);

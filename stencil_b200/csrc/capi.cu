@@ -11,7 +11,9 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "../../include/stencil_b200.h"
@@ -80,23 +82,35 @@ struct MapEntry {
     CUtensorMap map;
 };
 
+// Everything the library owns on ONE device.  A process binds one device (sb200_init) or a
+// group (sb200_init_multi); every host thread works on the State its thread-local pointer
+// names: the caller's thread on the first device of the group, the worker threads of a
+// multi-GPU sb200_run_host each on their own.
 struct State {
     bool ready = false;
     int device = -1;
     int sm_count = 0;
-    EncodeTiledFn encode = nullptr;
     std::vector<MapEntry> maps;
+    std::vector<const void*> attr_done;  // kernels whose launch attributes are set on this device
     // cached device buffers of sb200_run_host
     void* buf[2] = {nullptr, nullptr};
     size_t buf_bytes = 0;
     unsigned long long* d_acc = nullptr;
-    bool attr_set = false;
     // pipelined host path: dense staging image + copy-in / copy-out streams
     void* staging = nullptr;
     size_t staging_bytes = 0;
     cudaStream_t st_in = nullptr, st_out = nullptr, st_sweep[4] = {nullptr, nullptr, nullptr, nullptr};
-} S;
+};
+std::vector<State*> g_group;          // devices bound by this process, in slab order
+thread_local State* tls_state = nullptr;
+State g_unbound;                      // placeholder before sb200_init (device -1, not ready)
+EncodeTiledFn g_encode = nullptr;
 std::mutex g_mu;
+
+State& DS() {
+    if (tls_state) return *tls_state;
+    return g_group.empty() ? g_unbound : *g_group[0];
+}
 
 size_t esize(int dtype) { return dtype == SB200_F64 ? 8 : 4; }
 
@@ -113,6 +127,8 @@ int validate(const sb200_desc* d) {
     }
     if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_LINE1D)
         return fail(SB200_ERR_INVALID, "bad kernel selector %d", d->kernel);
+    if (d->ngpus > SB200_MAX_GPUS) return fail(SB200_ERR_INVALID, "ngpus must be 0..%d (got %u)", SB200_MAX_GPUS, d->ngpus);
+    if (d->flags & ~(uint32_t)SB200_FLAG_REASSOCIATE) return fail(SB200_ERR_INVALID, "unknown flag bits 0x%x", d->flags);
     return SB200_OK;
 }
 
@@ -136,37 +152,124 @@ Grid make_grid(const sb200_desc* d, uint32_t ghost) {
     return g;
 }
 
-int ensure_ready() {
-    if (S.ready) return SB200_OK;
-    int n = 0;
-    cudaError_t e = cudaGetDeviceCount(&n);
-    if (e != cudaSuccess || n == 0) {
+// Bring one device up: context, SM count, the TMA descriptor encoder, the checksum
+// accumulator and the streams of the pipelined host path (one-time costs belong here, not
+// in the first timed call).  Leaves `dev` the calling thread's current device.
+int bring_up(State& st, int dev) {
+    CU_TRY(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10)
+        return fail(SB200_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only",
+                    dev, prop.major, prop.minor);
+    st.device = dev;
+    st.sm_count = prop.multiProcessorCount;
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (!fn || qres != cudaDriverEntryPointSuccess)
+            return fail(SB200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+        g_encode = (EncodeTiledFn)fn;
+    }
+    CU_TRY(cudaMalloc(&st.d_acc, sizeof(unsigned long long)));
+    CU_TRY(cudaStreamCreateWithFlags(&st.st_in, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&st.st_out, cudaStreamNonBlocking));
+    for (auto& q : st.st_sweep) CU_TRY(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
+    st.ready = true;
+    return SB200_OK;
+}
+
+void tear_down(State& st) {
+    if (!st.ready) return;
+    cudaSetDevice(st.device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 2; ++i) {
+        if (st.buf[i]) cudaFree(st.buf[i]);
+        st.buf[i] = nullptr;
+    }
+    st.buf_bytes = 0;
+    if (st.d_acc) cudaFree(st.d_acc);
+    st.d_acc = nullptr;
+    if (st.staging) cudaFree(st.staging);
+    st.staging = nullptr;
+    st.staging_bytes = 0;
+    if (st.st_in) cudaStreamDestroy(st.st_in);
+    if (st.st_out) cudaStreamDestroy(st.st_out);
+    for (auto& q : st.st_sweep) {
+        if (q) cudaStreamDestroy(q);
+        q = nullptr;
+    }
+    st.st_in = st.st_out = nullptr;
+    st.maps.clear();
+    st.attr_done.clear();  // function attributes are per device context
+    st.ready = false;
+}
+
+int device_count_checked(int* n) {
+    // load every kernel when the context is created (not inside the first timed launch);
+    // has no effect if the process initialised CUDA before
+    setenv("CUDA_MODULE_LOADING", "EAGER", 0);
+    *n = 0;
+    cudaError_t e = cudaGetDeviceCount(n);
+    if (e != cudaSuccess || *n == 0) {
         cudaGetLastError();
         return fail(SB200_ERR_NO_DEVICE,
                     "no CUDA device available (%s); this backend has no CPU fallback",
                     e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
     }
-    if (S.device < 0) S.device = 0;
-    CU_TRY(cudaSetDevice(S.device));
-    cudaDeviceProp prop;
-    CU_TRY(cudaGetDeviceProperties(&prop, S.device));
-    if (prop.major != 10)
-        return fail(SB200_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only",
-                    S.device, prop.major, prop.minor);
-    S.sm_count = prop.multiProcessorCount;
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-    if (!fn || qres != cudaDriverEntryPointSuccess)
-        return fail(SB200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
-    S.encode = (EncodeTiledFn)fn;
-    CU_TRY(cudaMalloc(&S.d_acc, sizeof(unsigned long long)));
-    S.ready = true;
+    return SB200_OK;
+}
+
+// Bind `n` devices (devices == nullptr: 0..n-1).  Caller holds g_mu.
+int bind_group(int n, const int* devices) {
+    int have = 0;
+    if (int rc = device_count_checked(&have)) return rc;
+    if (n < 1 || n > SB200_MAX_GPUS) return fail(SB200_ERR_INVALID, "device group of %d (1..%d)", n, SB200_MAX_GPUS);
+    for (int i = 0; i < n; ++i) {
+        const int d = devices ? devices[i] : i;
+        if (d < 0 || d >= have) return fail(SB200_ERR_INVALID, "device %d of %d visible", d, have);
+        for (int j = 0; j < i; ++j)
+            if ((devices ? devices[j] : j) == d) return fail(SB200_ERR_INVALID, "device %d listed twice", d);
+    }
+    std::vector<State*> group;
+    int rc = SB200_OK;
+    for (int i = 0; i < n && rc == SB200_OK; ++i) {
+        group.push_back(new State);
+        rc = bring_up(*group.back(), devices ? devices[i] : i);
+    }
+    if (rc != SB200_OK) {
+        for (State* st : group) {
+            tear_down(*st);
+            delete st;
+        }
+        return rc;
+    }
+    g_group.swap(group);
+    tls_state = nullptr;
+    CU_TRY(cudaSetDevice(g_group[0]->device));
+    return SB200_OK;
+}
+
+int ensure_ready() {
+    if (DS().ready) return SB200_OK;
+    return bind_group(1, nullptr);  // a caller that never called sb200_init gets device 0
+}
+
+// Launch attributes are per (function, device context): remember them per State.
+template <class F>
+int set_smem_attr_once(F* kernel, size_t bytes) {
+    State& st = DS();
+    const void* key = reinterpret_cast<const void*>(kernel);
+    for (const void* k : st.attr_done)
+        if (k == key) return SB200_OK;
+    CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    st.attr_done.push_back(key);
     return SB200_OK;
 }
 
 int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap** out) {
-    for (auto& m : S.maps)
+    for (auto& m : DS().maps)
         if (m.key.ptr == ptr && m.key.dtype == dtype && m.key.px == g.pitch_x &&
             m.key.py == g.pitch_y && m.key.pl == g.planes) {
             *out = &m.map;
@@ -180,14 +283,14 @@ int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap*
     cuuint32_t box[3] = {(cuuint32_t)(dtype == SB200_F64 ? T3<double, 1>::BX : T3<float, 1>::BX),
                          (cuuint32_t)T3<double, 1>::BY, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = S.encode(&me.map, dtype == SB200_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+    CUresult r = g_encode(&me.map, dtype == SB200_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
                           3, const_cast<void*>(ptr), dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SB200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    if (S.maps.size() >= 64) S.maps.erase(S.maps.begin());
-    S.maps.push_back(me);
-    *out = &S.maps.back().map;
+    if (DS().maps.size() >= 64) DS().maps.erase(DS().maps.begin());
+    DS().maps.push_back(me);
+    *out = &DS().maps.back().map;
     return SB200_OK;
 }
 
@@ -196,17 +299,15 @@ int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, lo
                    long long oe, cudaStream_t st, const SlabLinkDev& link_in) {
     using C = T3<T, K>;
     if (oe <= ob) return SB200_OK;
-    static bool attr = false;
-    if (!attr) {
-        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-        CU_TRY(cudaFuncSetAttribute(sweep_tma3d_kernel<T, K, SHAPE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-        attr = true;
-    }
+    const bool linked = link_in.link_lo || link_in.link_hi;
+    if (int rc = linked ? set_smem_attr_once(sweep_tma3d_kernel<T, K, SHAPE, true>, C::SMEM)
+                        : set_smem_attr_once(sweep_tma3d_kernel<T, K, SHAPE, false>, C::SMEM))
+        return rc;
     const CUtensorMap* map = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, &map)) return rc;
-    const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, S.sm_count);
+    const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, DS().sm_count);
     const T avg = Avg<T>::value(SHAPE, 3, 1);
-    if (link_in.link_lo || link_in.link_hi) {
+    if (linked) {
         SlabLinkDev link = link_in;
         long long nc = p.nchunks;
         if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
@@ -300,9 +401,9 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_WARP2D:
             if (g.r > 1)
-                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, S.sm_count, st));
+                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, DS().sm_count, st));
             else
-                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, S.sm_count, st));
+                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, DS().sm_count, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
@@ -399,36 +500,38 @@ int sb200_device_count(void) {
 
 int sb200_init(int device) {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (S.ready && S.device == device) return SB200_OK;
-    if (S.ready) return fail(SB200_ERR_INVALID, "already bound to device %d (one process per GPU)", S.device);
-    S.device = device;
-    return ensure_ready();
+    if (g_group.size() == 1 && g_group[0]->device == device) return SB200_OK;
+    if (!g_group.empty())
+        return fail(SB200_ERR_INVALID, "already bound to %zu device(s) starting at %d; sb200_finalize first",
+                    g_group.size(), g_group[0]->device);
+    return bind_group(1, &device);
+}
+
+int sb200_init_multi(int n, const int* devices) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if ((int)g_group.size() == n) {
+        bool same = true;
+        for (int i = 0; i < n; ++i) same = same && g_group[(size_t)i]->device == (devices ? devices[i] : i);
+        if (same) return SB200_OK;
+    }
+    if (!g_group.empty())
+        return fail(SB200_ERR_INVALID, "already bound to %zu device(s); sb200_finalize first", g_group.size());
+    return bind_group(n, devices);
+}
+
+int sb200_group_size(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    return (int)g_group.size();
 }
 
 void sb200_finalize(void) {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (!S.ready) return;
-    cudaDeviceSynchronize();
-    for (int i = 0; i < 2; ++i) {
-        if (S.buf[i]) cudaFree(S.buf[i]);
-        S.buf[i] = nullptr;
+    for (State* st : g_group) {
+        tear_down(*st);
+        delete st;
     }
-    S.buf_bytes = 0;
-    if (S.d_acc) cudaFree(S.d_acc);
-    S.d_acc = nullptr;
-    if (S.staging) cudaFree(S.staging);
-    S.staging = nullptr;
-    S.staging_bytes = 0;
-    if (S.st_in) cudaStreamDestroy(S.st_in);
-    if (S.st_out) cudaStreamDestroy(S.st_out);
-    for (auto& q : S.st_sweep) {
-        if (q) cudaStreamDestroy(q);
-        q = nullptr;
-    }
-    S.st_in = S.st_out = nullptr;
-    S.maps.clear();
-    S.ready = false;
-    S.device = -1;
+    g_group.clear();
+    tls_state = nullptr;
 }
 
 int sb200_layout_for(const sb200_desc* desc, uint32_t ghost, sb200_layout* layout) {
@@ -566,8 +669,8 @@ int sb200_device_alloc(void** ptr, size_t bytes) {
 int sb200_device_free(void* ptr) {
     if (!ptr) return SB200_OK;
     std::lock_guard<std::mutex> lk(g_mu);
-    for (size_t i = 0; i < S.maps.size();)  // tensor maps of a freed buffer must not be reused
-        if (S.maps[i].key.ptr == ptr) S.maps.erase(S.maps.begin() + i); else ++i;
+    for (size_t i = 0; i < DS().maps.size();)  // tensor maps of a freed buffer must not be reused
+        if (DS().maps[i].key.ptr == ptr) DS().maps.erase(DS().maps.begin() + i); else ++i;
     CU_TRY(cudaFree(ptr));
     return SB200_OK;
 }
@@ -595,6 +698,8 @@ int sb200_ipc_open(const unsigned char handle[SB200_IPC_HANDLE_BYTES], void** de
 
 int sb200_ipc_close(void* dev_ptr) {
     if (!dev_ptr) return SB200_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
     CU_TRY(cudaIpcCloseMemHandle(dev_ptr));
     return SB200_OK;
 }
@@ -648,15 +753,15 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     int ntx, nty;
     if (desc->dtype == SB200_F64) {
         switch (steps) {
-            case 1: { auto p = t3_plan<double, 1>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
-            case 2: { auto p = t3_plan<double, 2>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
-            default: { auto p = t3_plan<double, 3>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 1: { auto p = t3_plan<double, 1>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 2: { auto p = t3_plan<double, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<double, 3>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
         }
     } else {
         switch (steps) {
-            case 1: { auto p = t3_plan<float, 1>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
-            case 2: { auto p = t3_plan<float, 2>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
-            default: { auto p = t3_plan<float, 3>(g.n[0], g.n[1], 1, S.sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 1: { auto p = t3_plan<float, 1>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            case 2: { auto p = t3_plan<float, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<float, 3>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
         }
     }
     if (arrivals) *arrivals = (uint32_t)(ntx * nty);
@@ -678,7 +783,7 @@ int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int in
     if (z_total) gn[desc->ndim - 1] = (long long)z_total;
     const long long total = g.elems();
     long long blocks = (total + 255) / 256;
-    if (blocks > S.sm_count * 32) blocks = S.sm_count * 32;
+    if (blocks > DS().sm_count * 32) blocks = DS().sm_count * 32;
     cudaStream_t st = (cudaStream_t)stream;
     if (desc->dtype == SB200_F64)
         fill_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((double*)grid, g, init == SB200_INIT_RANDOM, seed, gn[0], gn[1], gn[2], (long long)z_offset);
@@ -785,10 +890,20 @@ static int pipeline_streams() {
     return NS;
 }
 
+// One slab of a multi-GPU call, in outermost interior indices LOCAL to its sub-grid: the slab
+// downloads [own_lo, own_hi); planes outside are deep halo (see sb200_slab_plan).  The whole
+// grid on one GPU is the slab {0, n}.
+struct SlabRange {
+    long long own_lo, own_hi;
+};
+
 static void build_pipeline(const sb200_desc* desc, const Choice& c, const Grid& g, int C, int NS,
-                           std::vector<sb200_pipe_op>& ops) {
+                           std::vector<sb200_pipe_op>& ops, SlabRange own = {0, -1},
+                           uint32_t* zone_uploads = nullptr) {
     const long long n = outer_n(g), r = g.r, T = desc->iterations;
     const long long n_outer_padded = g.ndim == 3 ? g.planes : g.pitch_y;
+    if (own.own_hi < 0) own.own_hi = n;
+    const bool low_zone = own.own_lo > 0, high_zone = own.own_hi < n;
     // Starting edges Z_i: C-1 equal upload chunks, then a last parallelogram that starts with
     // zero width at the high end (a triangle growing to T*r planes).  Final regions
     // F_i = Z_i - T*r clipped at 0: parallelograms that drift out of the grid before step T
@@ -806,20 +921,37 @@ static void build_pipeline(const sb200_desc* desc, const Choice& c, const Grid& 
     for (long long b = 0; b < T / c.k; ++b) blocks.push_back(c.k);
     const size_t nb = blocks.size();
     auto add = [&](int kind, int stream, int par, int block, uint32_t steps, int src, long long lo, long long hi,
-                   int w0) {
+                   int w0, int w1 = -1) {
         sb200_pipe_op o;
         o.kind = kind; o.stream = stream; o.parallelogram = par; o.block = block; o.steps = steps; o.src = src;
-        o.lo = lo; o.hi = hi; o.wait[0] = w0; o.wait[1] = -1;
+        o.lo = lo; o.hi = hi; o.wait[0] = w0; o.wait[1] = w1;
         ops.push_back(o);
         return (int)ops.size() - 1;
     };
     ops.clear();
-    // upload chunk i = padded outer indices [U_i, U_i+1), all on the copy-in stream
-    std::vector<int> up(C);
+    // upload chunk i = padded outer indices [U_i, U_i+1), all on the copy-in stream.  A slab
+    // uploads its high deep-halo zone FIRST (and its low one is the start of chunk 0 anyway):
+    // those are the host planes a neighbouring slab downloads into when T is even, and the
+    // neighbours' downloads are held back until the zones have been read (zone_uploads).
+    const long long hz = high_zone ? own.own_hi + r : n_outer_padded;  // first padded index of the high zone
+    const int upH = high_zone ? add(SB200_PIPE_UPLOAD, 0, C - 1, -1, 0, -1, hz, n_outer_padded, -1) : -1;
+    std::vector<int> up(C, -1);
+    std::vector<char> needs_hz(C, 0);
+    uint32_t zones = high_zone ? 1 : 0;
+    bool low_covered = !low_zone;
     for (int i = 0; i < C; ++i) {
         const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
-        up[i] = add(SB200_PIPE_UPLOAD, 0, i, -1, 0, -1, ub, ue, -1);
+        const long long uc = ue < hz ? ue : hz;
+        if (uc > ub) {
+            up[i] = add(SB200_PIPE_UPLOAD, 0, i, -1, 0, -1, ub, uc, -1);
+            if (!low_covered) {
+                ++zones;
+                low_covered = uc >= own.own_lo + r;
+            }
+        }
+        needs_hz[i] = ue > hz;
     }
+    if (zone_uploads) *zone_uploads = zones;
     // Consecutive parallelograms alternate between the sweep streams and run as a wavefront:
     // block b of parallelogram i+1 only waits for block b-1 of parallelogram i (its slanted
     // left halo; the same edge orders the write-after-read on the ping-pong buffer), so the
@@ -830,7 +962,8 @@ static void build_pipeline(const sb200_desc* desc, const Choice& c, const Grid& 
     for (int i = 0; i < C; ++i) {
         const int ss = 2 + i % NS;
         const long long ub = i == 0 ? 0 : Z[i] + r, ue = i == C - 1 ? n_outer_padded : Z[i + 1] + r;
-        int last = add(SB200_PIPE_UNPACK, ss, i, -1, 0, -1, ub, ue, up[i]);
+        int last = add(SB200_PIPE_UNPACK, ss, i, -1, 0, -1, ub, ue, up[i] >= 0 ? up[i] : upH,
+                       up[i] >= 0 && needs_hz[i] ? upH : -1);
         cur_upto[0] = last;  // what "block -1" of this parallelogram means to its right neighbour
         long long done_steps = 0;
         for (size_t b = 0; b < nb; ++b) {
@@ -839,18 +972,35 @@ static void build_pipeline(const sb200_desc* desc, const Choice& c, const Grid& 
             long long R = i == C - 1 ? n : Z[i + 1] - done_steps * r;
             if (L < 0) L = 0;
             if (R > n) R = n;
+            // a slab only needs the dependency cone of the planes it owns: after `done` steps
+            // that is [own_lo - (T-done)*r, own_hi + (T-done)*r)
+            const long long need_lo = own.own_lo - (T - done_steps) * r, need_hi = own.own_hi + (T - done_steps) * r;
+            if (L < need_lo) L = need_lo;
+            if (R > need_hi) R = need_hi;
             if (R > L) last = add(SB200_PIPE_SWEEP, ss, i, (int)b, (uint32_t)blocks[b], (int)(b & 1), L, R,
                                   i > 0 ? prev_upto[b] : -1);
             cur_upto[b + 1] = last;
         }
-        if (F[i + 1] > F[i]) add(SB200_PIPE_DOWNLOAD, 1, i, -1, 0, (int)(nb & 1), F[i], F[i + 1], last);
+        const long long dl = F[i] > own.own_lo ? F[i] : own.own_lo, dh = F[i + 1] < own.own_hi ? F[i + 1] : own.own_hi;
+        if (dh > dl) add(SB200_PIPE_DOWNLOAD, 1, i, -1, 0, (int)(nb & 1), dl, dh, last);
         prev_upto.swap(cur_upto);
     }
 }
 
+// Cross-device ordering of one slab's host reads against its neighbours' host writes.
+struct SlabSync {
+    cudaEvent_t zones_read = nullptr;           // recorded by this slab after its zone uploads
+    cudaEvent_t wait[2] = {nullptr, nullptr};   // the neighbours' zones_read
+    void (*host_barrier)(void*) = nullptr;      // returns once EVERY slab has recorded zones_read
+    void* barrier_arg = nullptr;
+    uint32_t zone_uploads = 0;
+};
+
 static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in, void* out,
-                              sb200_timing* timing, int C) {
+                              sb200_timing* timing, int C, SlabRange own = {0, -1},
+                              const SlabSync* sync = nullptr) {
     const auto w0 = std::chrono::steady_clock::now();
+    State& D = DS();
     const Grid g = make_grid(desc, 0);
     const size_t es = esize(desc->dtype);
     const long long r = g.r;
@@ -859,23 +1009,18 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     const long long n_outer_padded = g.ndim == 3 ? g.planes : g.pitch_y;
     const size_t outer_bytes = (size_t)hx * rows_per_outer * es;  // dense bytes per outer index
     const size_t dense_bytes = outer_bytes * n_outer_padded;
-    if (S.staging_bytes < dense_bytes) {
-        if (S.staging) cudaFree(S.staging);
-        S.staging = nullptr;
-        S.staging_bytes = 0;
-        CU_TRY(cudaMalloc(&S.staging, dense_bytes));
-        S.staging_bytes = dense_bytes;
-    }
-    if (!S.st_in) {
-        CU_TRY(cudaStreamCreateWithFlags(&S.st_in, cudaStreamNonBlocking));
-        CU_TRY(cudaStreamCreateWithFlags(&S.st_out, cudaStreamNonBlocking));
-        for (auto& q : S.st_sweep) CU_TRY(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
+    if (D.staging_bytes < dense_bytes) {
+        if (D.staging) cudaFree(D.staging);
+        D.staging = nullptr;
+        D.staging_bytes = 0;
+        CU_TRY(cudaMalloc(&D.staging, dense_bytes));
+        D.staging_bytes = dense_bytes;
     }
     const int NS = pipeline_streams();
     std::vector<sb200_pipe_op> ops;
-    build_pipeline(desc, c, g, C, NS, ops);
+    build_pipeline(desc, c, g, C, NS, ops, own);
     cudaStream_t st = 0;  // the caller's stream: start / end of the whole pipeline
-    auto stream_of = [&](const sb200_pipe_op& o) { return o.stream == 0 ? S.st_in : o.stream == 1 ? S.st_out : S.st_sweep[o.stream - 2]; };
+    auto stream_of = [&](const sb200_pipe_op& o) { return o.stream == 0 ? D.st_in : o.stream == 1 ? D.st_out : D.st_sweep[o.stream - 2]; };
     // one event per op that another op waits for
     Events events;
     cudaEvent_t ev[4];
@@ -886,34 +1031,50 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
             if (w >= 0 && !op_done[(size_t)w]) op_done[(size_t)w] = events.make();
     CU_TRY(events.err);
     CU_TRY(cudaEventRecord(ev[0], st));
-    CU_TRY(cudaStreamWaitEvent(S.st_in, ev[0], 0));
-    CU_TRY(cudaStreamWaitEvent(S.st_out, ev[0], 0));
-    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(S.st_sweep[q], ev[0], 0));
+    CU_TRY(cudaStreamWaitEvent(D.st_in, ev[0], 0));
+    CU_TRY(cudaStreamWaitEvent(D.st_out, ev[0], 0));
+    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamWaitEvent(D.st_sweep[q], ev[0], 0));
     const Domain dom = make_domain(g, 1, 1);
-    void* buf[2] = {S.buf[0], S.buf[1]};
+    void* buf[2] = {D.buf[0], D.buf[1]};
     void* host_dst = (desc->iterations & 1u) ? out : in;
     uint32_t nl = 0;
     int uploads_left = 0;
     for (const auto& o : ops) uploads_left += o.kind == SB200_PIPE_UPLOAD;
     bool first_download = false;
+    // Uploads have no predecessors, so they are all issued first, in list order (they share the
+    // copy-in stream).  A slab then tells its neighbours when its deep-halo zones have been
+    // read, and holds its own downloads back until theirs have (T even: slabs download into
+    // the host array the others still upload from).
+    uint32_t uploads_issued = 0;
     for (size_t j = 0; j < ops.size(); ++j) {
         const sb200_pipe_op& o = ops[j];
+        if (o.kind != SB200_PIPE_UPLOAD) continue;
+        CU_TRY(cudaMemcpyAsync((char*)D.staging + o.lo * outer_bytes, (const char*)in + o.lo * outer_bytes,
+                               (size_t)(o.hi - o.lo) * outer_bytes, cudaMemcpyHostToDevice, D.st_in));
+        if (op_done[j]) CU_TRY(cudaEventRecord(op_done[j], D.st_in));
+        if (--uploads_left == 0) CU_TRY(cudaEventRecord(ev[1], D.st_in));
+        if (sync && ++uploads_issued == sync->zone_uploads) CU_TRY(cudaEventRecord(sync->zones_read, D.st_in));
+    }
+    if (sync) {
+        if (sync->zone_uploads == 0) CU_TRY(cudaEventRecord(sync->zones_read, D.st_in));
+        sync->host_barrier(sync->barrier_arg);  // every slab's zones_read is recorded from here on
+        for (cudaEvent_t e : sync->wait)
+            if (e) CU_TRY(cudaStreamWaitEvent(D.st_out, e, 0));
+    }
+    for (size_t j = 0; j < ops.size(); ++j) {
+        const sb200_pipe_op& o = ops[j];
+        if (o.kind == SB200_PIPE_UPLOAD) continue;
         cudaStream_t ss = stream_of(o);
         for (int w : o.wait)
             if (w >= 0) CU_TRY(cudaStreamWaitEvent(ss, op_done[(size_t)w], 0));
         switch (o.kind) {
-            case SB200_PIPE_UPLOAD:
-                CU_TRY(cudaMemcpyAsync((char*)S.staging + o.lo * outer_bytes, (const char*)in + o.lo * outer_bytes,
-                                       (size_t)(o.hi - o.lo) * outer_bytes, cudaMemcpyHostToDevice, ss));
-                if (--uploads_left == 0) CU_TRY(cudaEventRecord(ev[1], ss));
-                break;
             case SB200_PIPE_UNPACK: {
                 const long long rb = o.lo * rows_per_outer, re = o.hi * rows_per_outer;
                 dim3 grid((unsigned)((g.pitch_x + 255) / 256), (unsigned)((re - rb) < 65535 ? (re - rb) : 65535));
                 if (desc->dtype == SB200_F64)
-                    unpack_dense2_kernel<double><<<grid, 256, 0, ss>>>((const double*)S.staging, (double*)buf[0], (double*)buf[1], g, hx, rb, re);
+                    unpack_dense2_kernel<double><<<grid, 256, 0, ss>>>((const double*)D.staging, (double*)buf[0], (double*)buf[1], g, hx, rb, re);
                 else
-                    unpack_dense2_kernel<float><<<grid, 256, 0, ss>>>((const float*)S.staging, (float*)buf[0], (float*)buf[1], g, hx, rb, re);
+                    unpack_dense2_kernel<float><<<grid, 256, 0, ss>>>((const float*)D.staging, (float*)buf[0], (float*)buf[1], g, hx, rb, re);
                 CU_TRY(cudaGetLastError());
                 break;
             }
@@ -931,13 +1092,13 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         }
         if (op_done[j]) CU_TRY(cudaEventRecord(op_done[j], ss));
     }
-    if (!first_download) CU_TRY(cudaEventRecord(ev[2], S.st_out));
-    CU_TRY(cudaEventRecord(ev[3], S.st_out));
+    if (!first_download) CU_TRY(cudaEventRecord(ev[2], D.st_out));
+    CU_TRY(cudaEventRecord(ev[3], D.st_out));
     CU_TRY(cudaStreamWaitEvent(st, ev[3], 0));
-    CU_TRY(cudaStreamSynchronize(S.st_out));
-    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamSynchronize(S.st_sweep[q]));
+    CU_TRY(cudaStreamSynchronize(D.st_out));
+    for (int q = 0; q < NS; ++q) CU_TRY(cudaStreamSynchronize(D.st_sweep[q]));
     CU_TRY(cudaStreamSynchronize(st));
-    CU_TRY(cudaStreamSynchronize(S.st_in));
+    CU_TRY(cudaStreamSynchronize(D.st_in));
     const auto w1 = std::chrono::steady_clock::now();
     if (timing) {
         float ms = 0;
@@ -949,6 +1110,8 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         timing->time_block = (uint32_t)c.k;
         timing->kernel = c.kernel;
         timing->result_in_out = (int)(desc->iterations & 1u);
+        timing->ngpus = 1;
+        timing->pipelined = 1;
     }
     return SB200_OK;
 }
@@ -965,6 +1128,80 @@ int sb200_pipeline_schedule(const sb200_desc* desc, sb200_pipe_op* ops_out, uint
     if (C <= 1) return SB200_OK;  // not pipelined: upload, sweep, download back to back
     std::vector<sb200_pipe_op> ops;
     build_pipeline(desc, c, g, C, pipeline_streams(), ops);
+    *count = (uint32_t)ops.size();
+    if (ops.size() > capacity) return capacity ? fail(SB200_ERR_INVALID, "schedule has %zu ops, capacity %u", ops.size(), capacity) : SB200_OK;
+    memcpy(ops_out, ops.data(), ops.size() * sizeof(sb200_pipe_op));
+    return SB200_OK;
+}
+
+// ---- one call, N GPUs ---------------------------------------------------------------------
+// Slabs along the outermost axis with T*r planes of deep halo per internal side, read from
+// the caller's host array (the host holds the whole grid, so the halo costs PCIe bytes and
+// redundant sweeps of the shrinking cone, but no GPU ever waits for another one and every slab
+// keeps the pipelined upload / sweep / download schedule on its own PCIe link).
+static sb200_desc slab_desc(const sb200_desc* d, long long planes) {
+    sb200_desc s = *d;
+    s.n[d->ndim - 1] = (uint64_t)planes;
+    s.ngpus = 1;
+    return s;
+}
+
+static int slab_plan_impl(const sb200_desc* d, int ngpus, sb200_slab_plan* plan) {
+    memset(plan, 0, sizeof *plan);
+    const long long n = d->ndim >= 2 ? (long long)d->n[d->ndim - 1] : 1;
+    const long long h = (long long)d->iterations * d->radius;
+    plan->deep_halo = (uint32_t)h;
+    const Choice c = choose(d);
+    if (int rc = check_choice(d, c)) return rc;
+    int G = ngpus < 1 ? 1 : (ngpus > SB200_MAX_GPUS ? SB200_MAX_GPUS : ngpus);
+    if (d->ndim < 2 || d->iterations == 0 || c.kernel == SB200_KERNEL_RESIDENT2D) G = 1;
+    for (; G > 1; --G) {
+        // thick enough for the halo to stay a minority, and worth pipelining on its own
+        if (n / G < 2 * h || n / G < 8LL * c.k * d->radius) continue;
+        const long long sub = n / G + 2 * h;
+        const sb200_desc sd = slab_desc(d, sub);
+        const Grid g = make_grid(&sd, 0);
+        const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * esize(d->dtype);
+        if (pipeline_chunks(&sd, c, g, dense) > 1) break;
+    }
+    plan->ngpus_used = (uint32_t)G;
+    for (int i = 0; i < G; ++i) {
+        const long long lo = n * i / G, hi = n * (i + 1) / G;
+        plan->slab[i].own_lo = (uint64_t)lo;
+        plan->slab[i].own_hi = (uint64_t)hi;
+        plan->slab[i].sub_lo = (uint64_t)(G > 1 && lo - h > 0 ? lo - h : 0);
+        plan->slab[i].sub_hi = (uint64_t)(G > 1 && hi + h < n ? hi + h : n);
+    }
+    return SB200_OK;
+}
+
+int sb200_slab_plan_for(const sb200_desc* desc, int ngpus, sb200_slab_plan* plan) {
+    if (int rc = validate(desc)) return rc;
+    if (!plan) return fail(SB200_ERR_INVALID, "null plan");
+    return slab_plan_impl(desc, ngpus, plan);
+}
+
+int sb200_pipeline_schedule_slab(const sb200_desc* desc, int ngpus, int slab, sb200_pipe_op* ops_out,
+                                 uint32_t capacity, uint32_t* count, uint32_t* zone_uploads) {
+    if (int rc = validate(desc)) return rc;
+    if (!count || (capacity && !ops_out)) return fail(SB200_ERR_INVALID, "bad argument");
+    sb200_slab_plan plan;
+    if (int rc = slab_plan_impl(desc, ngpus, &plan)) return rc;
+    if (slab < 0 || slab >= (int)plan.ngpus_used) return fail(SB200_ERR_INVALID, "slab %d of %u", slab, plan.ngpus_used);
+    *count = 0;
+    if (zone_uploads) *zone_uploads = 0;
+    if (plan.ngpus_used < 2) return sb200_pipeline_schedule(desc, ops_out, capacity, count);
+    const auto& sl = plan.slab[slab];
+    const sb200_desc sd = slab_desc(desc, (long long)(sl.sub_hi - sl.sub_lo));
+    const Choice c = choose(&sd);
+    const Grid g = make_grid(&sd, 0);
+    const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * esize(sd.dtype);
+    const int C = pipeline_chunks(&sd, c, g, dense);
+    std::vector<sb200_pipe_op> ops;
+    uint32_t zones = 0;
+    build_pipeline(&sd, c, g, C, pipeline_streams(), ops,
+                   {(long long)(sl.own_lo - sl.sub_lo), (long long)(sl.own_hi - sl.sub_lo)}, &zones);
+    if (zone_uploads) *zone_uploads = zones;
     *count = (uint32_t)ops.size();
     if (ops.size() > capacity) return capacity ? fail(SB200_ERR_INVALID, "schedule has %zu ops, capacity %u", ops.size(), capacity) : SB200_OK;
     memcpy(ops_out, ops.data(), ops.size() * sizeof(sb200_pipe_op));
@@ -997,17 +1234,17 @@ int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* gr
     long long gn[3] = {g.n[0], g.n[1], g.n[2]};
     if (z_total) gn[desc->ndim - 1] = (long long)z_total;
     cudaStream_t st = (cudaStream_t)stream;
-    CU_TRY(cudaMemsetAsync(S.d_acc, 0, sizeof(unsigned long long), st));
+    CU_TRY(cudaMemsetAsync(DS().d_acc, 0, sizeof(unsigned long long), st));
     const long long total = g.n[0] * g.n[1] * g.n[2];
     long long blocks = (total + 255) / 256;
-    if (blocks > S.sm_count * 16) blocks = S.sm_count * 16;
+    if (blocks > DS().sm_count * 16) blocks = DS().sm_count * 16;
     if (desc->dtype == SB200_F64)
-        checksum_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((const double*)grid, g, gn[0], gn[1], (long long)z_offset, S.d_acc);
+        checksum_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((const double*)grid, g, gn[0], gn[1], (long long)z_offset, DS().d_acc);
     else
-        checksum_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)grid, g, gn[0], gn[1], (long long)z_offset, S.d_acc);
+        checksum_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)grid, g, gn[0], gn[1], (long long)z_offset, DS().d_acc);
     CU_TRY(cudaGetLastError());
     unsigned long long h = 0;
-    CU_TRY(cudaMemcpyAsync(&h, S.d_acc, sizeof h, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(&h, DS().d_acc, sizeof h, cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
     *out = (uint64_t)h;
     return SB200_OK;
@@ -1017,12 +1254,15 @@ int sb200_host_alloc(void** ptr, size_t bytes) {
     if (!ptr) return fail(SB200_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
-    CU_TRY(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
+    // portable: page-locked for every device of the group, not only the current one
+    CU_TRY(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
     return SB200_OK;
 }
 
 int sb200_host_free(void* ptr) {
     if (!ptr) return SB200_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
     CU_TRY(cudaFreeHost(ptr));
     return SB200_OK;
 }
@@ -1031,12 +1271,14 @@ int sb200_host_register(void* ptr, size_t bytes) {
     if (!ptr || bytes == 0) return fail(SB200_ERR_INVALID, "bad host range");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
-    CU_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    CU_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
     return SB200_OK;
 }
 
 int sb200_host_unregister(void* ptr) {
     if (!ptr) return SB200_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
     CU_TRY(cudaHostUnregister(ptr));
     return SB200_OK;
 }
@@ -1058,16 +1300,16 @@ static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timi
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t bytes = (size_t)g.elems() * esize(desc->dtype);
-    if (S.buf_bytes < bytes) {
+    if (DS().buf_bytes < bytes) {
         for (int i = 0; i < 2; ++i) {
-            if (S.buf[i]) cudaFree(S.buf[i]);
-            S.buf[i] = nullptr;
+            if (DS().buf[i]) cudaFree(DS().buf[i]);
+            DS().buf[i] = nullptr;
         }
-        S.buf_bytes = 0;
-        S.maps.clear();
-        CU_TRY(cudaMalloc(&S.buf[0], bytes));
-        CU_TRY(cudaMalloc(&S.buf[1], bytes));
-        S.buf_bytes = bytes;
+        DS().buf_bytes = 0;
+        DS().maps.clear();
+        CU_TRY(cudaMalloc(&DS().buf[0], bytes));
+        CU_TRY(cudaMalloc(&DS().buf[1], bytes));
+        DS().buf_bytes = bytes;
     }
     {
         const Choice c = choose(desc);
@@ -1093,30 +1335,30 @@ static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timi
     {
         const long long hx = g.n[0] + 2 * g.r;
         const size_t dense_bytes = (size_t)hx * g.pitch_y * g.planes * esize(desc->dtype);
-        void* staging = (char*)S.buf[1] + (bytes - dense_bytes);  // tail of buf[1]
+        void* staging = (char*)DS().buf[1] + (bytes - dense_bytes);  // tail of buf[1]
         CU_TRY(cudaMemcpyAsync(staging, in, dense_bytes, cudaMemcpyHostToDevice, st));
         // the staging image sits at the tail of buf[1]; unpack into buf[0], then clone
         // buf[0] over buf[1] (both reference matrices carry the same halo, stencil.cpp:190-207)
         const long long rows = g.pitch_y * g.planes;
         dim3 grid((unsigned)((g.pitch_x + 255) / 256), (unsigned)(rows < 65535 ? rows : 65535));
         if (desc->dtype == SB200_F64)
-            unpack_dense_kernel<double><<<grid, 256, 0, st>>>((const double*)staging, (double*)S.buf[0], g, hx);
+            unpack_dense_kernel<double><<<grid, 256, 0, st>>>((const double*)staging, (double*)DS().buf[0], g, hx);
         else
-            unpack_dense_kernel<float><<<grid, 256, 0, st>>>((const float*)staging, (float*)S.buf[0], g, hx);
+            unpack_dense_kernel<float><<<grid, 256, 0, st>>>((const float*)staging, (float*)DS().buf[0], g, hx);
         CU_TRY(cudaGetLastError());
-        CU_TRY(cudaMemcpyAsync(S.buf[1], S.buf[0], bytes, cudaMemcpyDeviceToDevice, st));
+        CU_TRY(cudaMemcpyAsync(DS().buf[1], DS().buf[0], bytes, cudaMemcpyDeviceToDevice, st));
     }
     CU_TRY(cudaEventRecord(ev[1], st));
     int in_b = 0;
     uint32_t nl = 0, used_k = 0;
     int used_kernel = 0;
-    if (int rc = sweep_impl(desc, 0, 1, 1, S.buf[0], S.buf[1], desc->iterations, st, &in_b, &nl, &used_k, &used_kernel))
+    if (int rc = sweep_impl(desc, 0, 1, 1, DS().buf[0], DS().buf[1], desc->iterations, st, &in_b, &nl, &used_k, &used_kernel))
         return rc;
     CU_TRY(cudaEventRecord(ev[2], st));
     // Step T belongs in `out` when T is odd, in `in` when even (stencil.cpp:88-92,129-134).
     void* host_dst = (desc->iterations & 1u) ? out : in;
     if (desc->iterations > 0)
-        if (int rc = copy_grid(desc, 0, S.buf[in_b], host_dst, false, true, st)) return rc;
+        if (int rc = copy_grid(desc, 0, DS().buf[in_b], host_dst, false, true, st)) return rc;
     CU_TRY(cudaEventRecord(ev[3], st));
     CU_TRY(cudaStreamSynchronize(st));
     const auto w1 = std::chrono::steady_clock::now();
