@@ -27,7 +27,11 @@ SYMBOLS = [
     "sb200_device_alloc", "sb200_device_free", "sb200_ipc_export", "sb200_ipc_open",
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
     "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
+    "sb200_init_multi", "sb200_group_size", "sb200_prepare", "sb200_slab_plan_for",
+    "sb200_pipeline_schedule_slab",
 ]
+MAX_GPUS = 16
+FLAG_REASSOCIATE = 1
 PIPE_UPLOAD, PIPE_UNPACK, PIPE_SWEEP, PIPE_DOWNLOAD = 0, 1, 2, 3
 IPC_HANDLE_BYTES = 64
 LINK_FLAG_WORDS = 4
@@ -39,6 +43,7 @@ class Desc(ctypes.Structure):
         ("radius", ctypes.c_uint32), ("n", ctypes.c_uint64 * 3),
         ("iterations", ctypes.c_uint32), ("time_block", ctypes.c_uint32),
         ("block_hint", ctypes.c_uint32), ("kernel", ctypes.c_int32),
+        ("ngpus", ctypes.c_uint32), ("flags", ctypes.c_uint32),
     ]
 
 
@@ -47,7 +52,7 @@ class Timing(ctypes.Structure):
         ("h2d_ms", ctypes.c_double), ("sweep_ms", ctypes.c_double), ("d2h_ms", ctypes.c_double),
         ("wall_ms", ctypes.c_double), ("launches", ctypes.c_uint32),
         ("time_block", ctypes.c_uint32), ("kernel", ctypes.c_int32),
-        ("result_in_out", ctypes.c_int32),
+        ("result_in_out", ctypes.c_int32), ("ngpus", ctypes.c_uint32), ("pipelined", ctypes.c_uint32),
     ]
 
 
@@ -73,6 +78,15 @@ class PlanInfo(ctypes.Structure):
         ("tiles_x", ctypes.c_uint32), ("tiles_y", ctypes.c_uint32), ("chunks", ctypes.c_uint32),
         ("chunk_extent", ctypes.c_uint32), ("pipeline_chunks", ctypes.c_uint32),
     ]
+
+
+class _Slab(ctypes.Structure):
+    _fields_ = [("sub_lo", ctypes.c_uint64), ("sub_hi", ctypes.c_uint64),
+                ("own_lo", ctypes.c_uint64), ("own_hi", ctypes.c_uint64)]
+
+
+class SlabPlan(ctypes.Structure):
+    _fields_ = [("ngpus_used", ctypes.c_uint32), ("deep_halo", ctypes.c_uint32), ("slab", _Slab * MAX_GPUS)]
 
 
 class PipeOp(ctypes.Structure):
@@ -107,6 +121,12 @@ def lib() -> ctypes.CDLL:
         L.sb200_last_error.restype = ctypes.c_char_p
         L.sb200_device_count.restype = i32
         L.sb200_init.argtypes = [i32]
+        L.sb200_init_multi.argtypes = [i32, ctypes.POINTER(i32)]
+        L.sb200_group_size.restype = i32
+        L.sb200_prepare.argtypes = [dp]
+        L.sb200_slab_plan_for.argtypes = [dp, i32, ctypes.POINTER(SlabPlan)]
+        L.sb200_pipeline_schedule_slab.argtypes = [dp, i32, i32, ctypes.POINTER(PipeOp), u32,
+                                                   ctypes.POINTER(u32), ctypes.POINTER(u32)]
         L.sb200_finalize.restype = None
         L.sb200_run_host.argtypes = [dp, vp, vp, ctypes.POINTER(Timing)]
         L.sb200_layout_for.argtypes = [dp, u32, ctypes.POINTER(Layout)]
@@ -144,7 +164,7 @@ def check(rc: int) -> int:
 
 
 def make_desc(n, radius=1, shape=STAR, dtype=F32, iterations=1, time_block=0, block_hint=0,
-              kernel=KERNEL_AUTO) -> Desc:
+              kernel=KERNEL_AUTO, ngpus=0, flags=0) -> Desc:
     """n = (nx,), (nx, ny) or (nx, ny, nz) interior extents, x fastest."""
     n = tuple(int(v) for v in n)
     d = Desc()
@@ -153,6 +173,7 @@ def make_desc(n, radius=1, shape=STAR, dtype=F32, iterations=1, time_block=0, bl
     for a in range(3):
         d.n[a] = n[a] if a < len(n) else 1
     d.iterations, d.time_block, d.block_hint, d.kernel = iterations, time_block, block_hint, kernel
+    d.ngpus, d.flags = ngpus, flags
     return d
 
 
@@ -172,6 +193,24 @@ def pipeline_schedule(desc: Desc) -> list:
     ops = (PipeOp * n.value)()
     check(lib().sb200_pipeline_schedule(ctypes.byref(desc), ops, n.value, ctypes.byref(n)))
     return list(ops)
+
+
+def slab_plan(desc: Desc, ngpus: int) -> SlabPlan:
+    """How sb200_run_host would spread `desc` over `ngpus` devices (host logic only)."""
+    p = SlabPlan()
+    check(lib().sb200_slab_plan_for(ctypes.byref(desc), ngpus, ctypes.byref(p)))
+    return p
+
+
+def pipeline_schedule_slab(desc: Desc, ngpus: int, slab: int):
+    """(ops, zone_uploads) of one slab of a multi-GPU sb200_run_host; host logic only."""
+    n, z = ctypes.c_uint32(0), ctypes.c_uint32(0)
+    check(lib().sb200_pipeline_schedule_slab(ctypes.byref(desc), ngpus, slab, None, 0, ctypes.byref(n), ctypes.byref(z)))
+    if n.value == 0:
+        return [], 0
+    ops = (PipeOp * n.value)()
+    check(lib().sb200_pipeline_schedule_slab(ctypes.byref(desc), ngpus, slab, ops, n.value, ctypes.byref(n), ctypes.byref(z)))
+    return list(ops), z.value
 
 
 def plan(desc: Desc, steps: int, sm_count: int = 148) -> PlanInfo:

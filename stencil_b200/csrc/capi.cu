@@ -1284,33 +1284,279 @@ int sb200_host_unregister(void* ptr) {
 }
 
 static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timing* timing);
+static int run_host_multi(const sb200_desc* desc, const sb200_slab_plan& plan, void* in, void* out,
+                          sb200_timing* timing);
+
+// Both ping-pong grids of the host path on the calling thread's device (cached across calls).
+static int ensure_grids(size_t bytes) {
+    State& D = DS();
+    if (D.buf_bytes >= bytes) return SB200_OK;
+    for (int i = 0; i < 2; ++i) {
+        if (D.buf[i]) cudaFree(D.buf[i]);
+        D.buf[i] = nullptr;
+    }
+    D.buf_bytes = 0;
+    D.maps.clear();
+    CU_TRY(cudaMalloc(&D.buf[0], bytes));
+    CU_TRY(cudaMalloc(&D.buf[1], bytes));
+    D.buf_bytes = bytes;
+    return SB200_OK;
+}
+
+// The precondition of the host path: `out` carries the same halo as `in`.  Checked on a
+// sample of halo cells spread over every face (a full compare would read both arrays once
+// more on the host).  Returns the number of sampled cells that differ.
+static int halo_sample_mismatches(const sb200_desc* d, const void* in, const void* out) {
+    const long long r = d->radius;
+    long long ext[3] = {1, 1, 1}, stride[3] = {0, 0, 0};
+    long long s = 1;
+    for (int a = 0; a < d->ndim; ++a) {
+        ext[a] = (long long)d->n[a] + 2 * r;
+        stride[a] = s;
+        s *= ext[a];
+    }
+    const size_t es = esize(d->dtype);
+    int bad = 0;
+    for (int a = 0; a < d->ndim; ++a)
+        for (int side = 0; side < 2; ++side)
+            for (int smp = 0; smp < 16; ++smp) {
+                // a pseudo-random cell of this face: coordinate `a` inside the halo, the rest anywhere
+                uint64_t h = mix64_seeded(0x5b200u + (uint64_t)a * 2 + side, (uint64_t)smp);
+                long long off = 0;
+                for (int b = 0; b < d->ndim; ++b) {
+                    long long c;
+                    if (b == a) c = (side ? ext[b] - r : 0) + (long long)(h % (uint64_t)r);
+                    else c = (long long)(h % (uint64_t)ext[b]);
+                    h = mix64(h);
+                    off += c * stride[b];
+                }
+                bad += memcmp((const char*)in + (size_t)off * es, (const char*)out + (size_t)off * es, es) != 0;
+            }
+    return bad;
+}
 
 int sb200_run_host(const sb200_desc* desc, void* in, void* out, sb200_timing* timing) {
     if (int rc = validate(desc)) return rc;
     if (!in || !out) return fail(SB200_ERR_INVALID, "null host buffer");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
-    const int rc = run_host_impl(desc, in, out, timing);
-    // an error return may leave a copy from / to the caller's host buffers in flight
-    if (rc != SB200_OK) cudaDeviceSynchronize();
+    if (const int bad = halo_sample_mismatches(desc, in, out))
+        return fail(SB200_ERR_INVALID, "the halo of `out` differs from the halo of `in` (%d of the sampled cells): "
+                                       "both buffers must carry the same Dirichlet halo", bad);
+    tls_state = nullptr;  // the caller's thread works on the first device of the group
+    const int have = (int)g_group.size();
+    const int want = desc->ngpus == 0 ? have : (int)desc->ngpus;
+    if (want > have)
+        return fail(SB200_ERR_INVALID, "ngpus = %d but %d device(s) are bound (sb200_init_multi)", want, have);
+    int rc;
+    sb200_slab_plan plan;
+    if (want > 1 && (rc = slab_plan_impl(desc, want, &plan)) != SB200_OK) return rc;
+    if (want > 1 && plan.ngpus_used > 1) {
+        rc = run_host_multi(desc, plan, in, out, timing);
+    } else {
+        CU_TRY(cudaSetDevice(DS().device));
+        rc = run_host_impl(desc, in, out, timing);
+        // an error return may leave a copy from / to the caller's host buffers in flight
+        if (rc != SB200_OK) cudaDeviceSynchronize();
+    }
     return rc;
+}
+
+// Untimed preparation of everything sb200_run_host(desc) needs, on every device it will use:
+// ping-pong grids, the staging image, kernel attributes, and one warm-up launch of each
+// kernel variant the call will take (fused depth k and the remainder T mod k).
+static int prepare_on_current(const sb200_desc* sd) {
+    const Grid g = make_grid(sd, 0);
+    const size_t es = esize(sd->dtype);
+    if (int rc = ensure_grids((size_t)g.elems() * es)) return rc;
+    State& D = DS();
+    const Choice c = choose(sd);
+    if (int rc = check_choice(sd, c)) return rc;
+    const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * es;
+    if (pipeline_chunks(sd, c, g, dense) > 1 && D.staging_bytes < dense) {
+        if (D.staging) cudaFree(D.staging);
+        D.staging = nullptr;
+        D.staging_bytes = 0;
+        CU_TRY(cudaMalloc(&D.staging, dense));
+        D.staging_bytes = dense;
+    }
+    CU_TRY(cudaMemsetAsync(D.buf[0], 0, (size_t)g.elems() * es, 0));
+    CU_TRY(cudaMemsetAsync(D.buf[1], 0, (size_t)g.elems() * es, 0));
+    const uint32_t T = sd->iterations;
+    if (T > 0) {
+        const bool resident = c.kernel == SB200_KERNEL_RESIDENT2D ||
+                              (sd->kernel == SB200_KERNEL_AUTO && sd->time_block == 0 && c.kernel == SB200_KERNEL_WARP2D &&
+                               sd->radius == 1 && T >= 16 && resident2d_fits(g.n[0], g.n[1], (int)es));
+        if (resident) {
+            CU_TRY(launch_resident2d(D.buf[0], D.buf[1], g, sd->shape, (int)es, 1, 0));
+        } else {
+            const Domain dom = make_domain(g, 1, 1);
+            const long long n = outer_n(g);
+            const long long oe = n < 8LL * c.k * g.r ? n : 8LL * c.k * g.r;
+            const uint32_t ks[2] = {T < (uint32_t)c.k ? T : (uint32_t)c.k, T % (uint32_t)c.k};
+            for (uint32_t k : ks)
+                if (k)
+                    if (int rc = pass(sd, c, g, dom, D.buf[0], D.buf[1], (int)k, 0, oe, 0)) return rc;
+        }
+    }
+    CU_TRY(cudaDeviceSynchronize());
+    return SB200_OK;
+}
+
+int sb200_prepare(const sb200_desc* desc) {
+    if (int rc = validate(desc)) return rc;
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    const int have = (int)g_group.size();
+    const int want = desc->ngpus == 0 ? have : (int)desc->ngpus;
+    if (want > have)
+        return fail(SB200_ERR_INVALID, "ngpus = %d but %d device(s) are bound (sb200_init_multi)", want, have);
+    sb200_slab_plan plan;
+    if (int rc = slab_plan_impl(desc, want, &plan)) return rc;
+    int rc = SB200_OK;
+    for (uint32_t i = 0; i < plan.ngpus_used && rc == SB200_OK; ++i) {
+        const sb200_desc sd = plan.ngpus_used > 1
+                                  ? slab_desc(desc, (long long)(plan.slab[i].sub_hi - plan.slab[i].sub_lo))
+                                  : *desc;
+        tls_state = g_group[i];
+        rc = cudaSetDevice(g_group[i]->device) == cudaSuccess ? prepare_on_current(&sd)
+                                                               : fail(SB200_ERR_CUDA, "cudaSetDevice(%d) failed", g_group[i]->device);
+    }
+    tls_state = nullptr;
+    cudaSetDevice(g_group[0]->device);
+    return rc;
+}
+
+// Host-side rendezvous of the slab worker threads (C++17: no std::barrier).
+struct HostBarrier {
+    std::mutex mu;
+    std::condition_variable cv;
+    int expected, arrived = 0;
+    explicit HostBarrier(int n) : expected(n) {}
+    void arrive_and_wait() {
+        std::unique_lock<std::mutex> lk(mu);
+        ++arrived;
+        cv.notify_all();
+        cv.wait(lk, [&] { return arrived >= expected; });
+    }
+    void abandon() {  // a worker that failed before the rendezvous must not hang the others
+        std::lock_guard<std::mutex> lk(mu);
+        --expected;
+        cv.notify_all();
+    }
+};
+
+struct SlabWorker {
+    State* st = nullptr;
+    sb200_desc sd;
+    void* in = nullptr;
+    void* out = nullptr;
+    SlabRange own{0, -1};
+    SlabSync sync;
+    HostBarrier* barrier = nullptr;
+    bool met = false;
+    sb200_timing tm;
+    int rc = SB200_OK;
+    char err[560];
+};
+
+static void slab_barrier_cb(void* arg) {
+    SlabWorker* w = (SlabWorker*)arg;
+    w->met = true;
+    w->barrier->arrive_and_wait();
+}
+
+static int slab_worker_body(SlabWorker& w) {
+    tls_state = w.st;
+    CU_TRY(cudaSetDevice(w.st->device));
+    const Grid g = make_grid(&w.sd, 0);
+    if (int rc = ensure_grids((size_t)g.elems() * esize(w.sd.dtype))) return rc;
+    const Choice c = choose(&w.sd);
+    const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * esize(w.sd.dtype);
+    const int C = pipeline_chunks(&w.sd, c, g, dense);
+    if (C < 2) return fail(SB200_ERR_INVALID, "slab of %lld planes cannot be pipelined", outer_n(g));
+    return run_host_pipelined(&w.sd, c, w.in, w.out, &w.tm, C, w.own, &w.sync);
+}
+
+static void slab_worker_main(SlabWorker* w) {
+    memset(&w->tm, 0, sizeof w->tm);
+    w->rc = slab_worker_body(*w);
+    if (w->rc != SB200_OK) {
+        snprintf(w->err, sizeof w->err, "GPU %d: %.500s", w->st->device, g_err);
+        if (!w->met) w->barrier->abandon();
+        cudaDeviceSynchronize();  // nothing of this slab may still touch the caller's buffers
+    }
+    tls_state = nullptr;
+}
+
+static int run_host_multi(const sb200_desc* desc, const sb200_slab_plan& plan, void* in, void* out,
+                          sb200_timing* timing) {
+    const auto w0 = std::chrono::steady_clock::now();
+    const int G = (int)plan.ngpus_used;
+    const long long r = desc->radius;
+    const size_t es = esize(desc->dtype);
+    // dense host bytes per outermost index (host layout: boundary_matrix.hpp:54-59,115-123)
+    const size_t outer_bytes = (size_t)(desc->n[0] + 2 * r) * (desc->ndim == 3 ? (size_t)(desc->n[1] + 2 * r) : 1) * es;
+    HostBarrier barrier(G);
+    std::vector<SlabWorker> ws((size_t)G);
+    Events events;  // the slabs' zones_read events; destroyed after the threads have joined
+    for (int i = 0; i < G; ++i) {
+        SlabWorker& w = ws[(size_t)i];
+        const auto& sl = plan.slab[i];
+        w.st = g_group[(size_t)i];
+        w.sd = slab_desc(desc, (long long)(sl.sub_hi - sl.sub_lo));
+        w.in = (char*)in + (size_t)sl.sub_lo * outer_bytes;
+        w.out = (char*)out + (size_t)sl.sub_lo * outer_bytes;
+        w.own = {(long long)(sl.own_lo - sl.sub_lo), (long long)(sl.own_hi - sl.sub_lo)};
+        w.barrier = &barrier;
+        w.sync.host_barrier = slab_barrier_cb;
+        w.sync.barrier_arg = &w;
+        CU_TRY(cudaSetDevice(w.st->device));
+        w.sync.zones_read = events.make();
+        CU_TRY(events.err);
+        {   // how many leading uploads cover the deep-halo zones (same builder the worker runs)
+            const Choice c = choose(&w.sd);
+            const Grid g = make_grid(&w.sd, 0);
+            const size_t dense = (size_t)(g.n[0] + 2 * g.r) * g.pitch_y * g.planes * es;
+            const int C = pipeline_chunks(&w.sd, c, g, dense);
+            std::vector<sb200_pipe_op> ops;
+            if (C > 1) build_pipeline(&w.sd, c, g, C, pipeline_streams(), ops, w.own, &w.sync.zone_uploads);
+        }
+    }
+    for (int i = 0; i < G; ++i) {
+        if (i > 0) ws[(size_t)i].sync.wait[0] = ws[(size_t)i - 1].sync.zones_read;
+        if (i + 1 < G) ws[(size_t)i].sync.wait[1] = ws[(size_t)i + 1].sync.zones_read;
+    }
+    CU_TRY(cudaSetDevice(g_group[0]->device));
+    std::vector<std::thread> threads;
+    for (int i = 0; i < G; ++i) threads.emplace_back(slab_worker_main, &ws[(size_t)i]);
+    for (auto& t : threads) t.join();
+    const auto w1 = std::chrono::steady_clock::now();
+    for (const SlabWorker& w : ws)
+        if (w.rc != SB200_OK) return fail(w.rc, "%s", w.err);
+    if (timing) {
+        memset(timing, 0, sizeof *timing);
+        for (const SlabWorker& w : ws) {
+            timing->h2d_ms = w.tm.h2d_ms > timing->h2d_ms ? w.tm.h2d_ms : timing->h2d_ms;
+            timing->sweep_ms = w.tm.sweep_ms > timing->sweep_ms ? w.tm.sweep_ms : timing->sweep_ms;
+            timing->d2h_ms = w.tm.d2h_ms > timing->d2h_ms ? w.tm.d2h_ms : timing->d2h_ms;
+            timing->launches += w.tm.launches;
+        }
+        timing->wall_ms = std::chrono::duration<double, std::milli>(w1 - w0).count();
+        timing->time_block = ws[0].tm.time_block;
+        timing->kernel = ws[0].tm.kernel;
+        timing->result_in_out = (int)(desc->iterations & 1u);
+        timing->ngpus = (uint32_t)G;
+        timing->pipelined = 1;
+    }
+    return SB200_OK;
 }
 
 static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timing* timing) {
     const auto w0 = std::chrono::steady_clock::now();
     const Grid g = make_grid(desc, 0);
     const size_t bytes = (size_t)g.elems() * esize(desc->dtype);
-    if (DS().buf_bytes < bytes) {
-        for (int i = 0; i < 2; ++i) {
-            if (DS().buf[i]) cudaFree(DS().buf[i]);
-            DS().buf[i] = nullptr;
-        }
-        DS().buf_bytes = 0;
-        DS().maps.clear();
-        CU_TRY(cudaMalloc(&DS().buf[0], bytes));
-        CU_TRY(cudaMalloc(&DS().buf[1], bytes));
-        DS().buf_bytes = bytes;
-    }
+    if (int rc = ensure_grids(bytes)) return rc;
     {
         const Choice c = choose(desc);
         if (int rc = check_choice(desc, c)) return rc;
@@ -1372,6 +1618,8 @@ static int run_host_impl(const sb200_desc* desc, void* in, void* out, sb200_timi
         timing->time_block = used_k;
         timing->kernel = used_kernel;
         timing->result_in_out = (int)(desc->iterations & 1u);
+        timing->ngpus = 1;
+        timing->pipelined = 0;
     }
     return SB200_OK;
 }

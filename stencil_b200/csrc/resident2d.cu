@@ -12,15 +12,13 @@ template <class T, int SHAPE, int R, bool CLUSTER>
 cudaError_t launch_one(const T* in, T* out, const Grid& g, int steps, const RsPlan& p, cudaStream_t st) {
     auto kern = sweep_resident2d_kernel<T, SHAPE, R, CLUSTER>;
     const size_t smem = 2 * RS_WARPS * sizeof(RsInbox<T>);
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // function attributes belong to the current device's context, and this is one launch per
+    // call: set them every time rather than caching per process (sb200_init_multi, re-init)
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    if (CLUSTER) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e != cudaSuccess) return e;
-        if (CLUSTER) {
-            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            if (e != cudaSuccess) return e;
-        }
-        attr = true;
     }
     const T avg = Avg<T>::value(SHAPE, 2, 1);
     cudaLaunchConfig_t cfg = {};
