@@ -20,12 +20,13 @@ def test_header_symbols_all_exported(built):
     L = capi.lib()
     for s in declared:
         assert getattr(L, s) is not None
-    assert L.sb200_abi_version() == 3
+    assert L.sb200_abi_version() == 4
 
 
 def test_struct_sizes_match_header(built):
-    assert ctypes.sizeof(capi.Desc) == 56
-    assert ctypes.sizeof(capi.Timing) == 48
+    assert ctypes.sizeof(capi.Desc) == 64
+    assert ctypes.sizeof(capi.Timing) == 56
+    assert ctypes.sizeof(capi.SlabPlan) == 8 + 32 * capi.MAX_GPUS
     assert ctypes.sizeof(capi.Layout) == 56
     assert ctypes.sizeof(capi.SlabLink) == 48   # 5 pointers + uint32 (+ padding)
     assert ctypes.sizeof(capi.PlanInfo) == 32

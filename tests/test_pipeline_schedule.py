@@ -258,3 +258,174 @@ def test_random_shapes_race_free_and_correct(built, monkeypatch):
         _check_race_free(ops, n[-1], r, T)
         _execute(ops, _random_order(ops, rng), n, r, shape, dtype, T, seed=rng.randrange(1, 1000))
     assert pipelined >= 30
+
+
+# ---- one call, N GPUs: slab schedules (sb200_slab_plan_for / sb200_pipeline_schedule_slab) ----
+
+def _slab_setup(monkeypatch, n, r, shape, dtype, T, C, NS, G):
+    monkeypatch.setenv("SB200_PIPELINE_CHUNKS", str(C))
+    monkeypatch.setenv("SB200_PIPELINE_STREAMS", str(NS))
+    d = capi.make_desc(n, radius=r, shape=shape, dtype=dtype, iterations=T)
+    plan = capi.slab_plan(d, G)
+    slabs = []
+    for g in range(plan.ngpus_used):
+        ops, zones = capi.pipeline_schedule_slab(d, G, g)
+        slabs.append((plan.slab[g], ops, zones))
+    return plan, slabs
+
+
+def _check_slab_structure(sl, ops, zones, r):
+    sub_n = sl.sub_hi - sl.sub_lo
+    padded = sub_n + 2 * r
+    for kind in (U, P):
+        seen = np.zeros(padded, int)
+        for o in ops:
+            if o.kind == kind:
+                assert 0 <= o.lo < o.hi <= padded
+                seen[o.lo:o.hi] += 1
+        assert (seen == 1).all()
+    seen = np.zeros(sub_n, int)
+    for o in ops:
+        if o.kind == D:
+            seen[o.lo:o.hi] += 1
+    want = np.zeros(sub_n, int)
+    want[sl.own_lo - sl.sub_lo:sl.own_hi - sl.sub_lo] = 1
+    assert (seen == want).all(), "a slab downloads exactly the planes it owns"
+    ups = [o for o in ops if o.kind == U]
+    assert [o for o in ops[:len(ups)] if o.kind != U] == [], "uploads lead the list (they are issued first)"
+    # the leading `zones` uploads cover both deep-halo zones
+    cov = np.zeros(padded, int)
+    for o in ups[:zones]:
+        cov[o.lo:o.hi] = 1
+    lo_zone, hi_zone = sl.own_lo - sl.sub_lo, sl.own_hi - sl.sub_lo
+    if lo_zone > 0:
+        assert cov[:lo_zone + r].all()
+    if hi_zone < sub_n:
+        assert cov[hi_zone + r:].all()
+
+
+def _execute_slabs(plan, slabs, n, r, shape, dtype, T, rng, seed=5):
+    """All slabs on ONE pair of host arrays, ops interleaved in a random order that respects each
+    slab's happens-before plus the cross-device rule (a slab's downloads start after its
+    neighbours' zone uploads); the result must be the plain T-step sweep of the whole grid."""
+    code = oracle.F64 if dtype == capi.F64 else oracle.F32
+    host_in = oracle.fill(n, r, code, oracle.INIT_RANDOM, seed)
+    host_out = oracle.fill(n, r, code, oracle.INIT_REF)
+    want_a, want_b = host_in.copy(), host_out.copy()
+    want = want_b if oracle.sweep(n, r, shape, T, want_a, want_b) else want_a
+    host_dst = host_out if T & 1 else host_in
+    inner = (slice(None),) + tuple(slice(r, s - r) for s in host_in.shape[1:])
+    state = []
+    nodes, preds = [], {}
+    for g, (sl, ops, zones) in enumerate(slabs):
+        sub_n = sl.sub_hi - sl.sub_lo
+        shp = (sub_n + 2 * r,) + host_in.shape[1:]
+        state.append(dict(staging=np.full(shp, np.nan, host_in.dtype),
+                          g=[np.full(shp, np.nan, host_in.dtype), np.full(shp, np.nan, host_in.dtype)],
+                          n=tuple(n[:-1]) + (sub_n,)))
+        p = _preds(ops)
+        ups = [j for j, o in enumerate(ops) if o.kind == U]
+        for j in range(len(ops)):
+            nodes.append((g, j))
+            preds[(g, j)] = [(g, q) for q in set(p[j])]
+    for g, (sl, ops, zones) in enumerate(slabs):
+        for j, o in enumerate(ops):
+            if o.kind == D:
+                for nb in (g - 1, g + 1):
+                    if 0 <= nb < len(slabs):
+                        nb_ups = [q for q, oo in enumerate(slabs[nb][1]) if oo.kind == U]
+                        if slabs[nb][2]:
+                            preds[(g, j)].append((nb, nb_ups[slabs[nb][2] - 1]))
+    indeg = {v: len(set(p)) for v, p in preds.items()}
+    succ = {v: [] for v in nodes}
+    for v, p in preds.items():
+        for q in set(p):
+            succ[q].append(v)
+    ready = [v for v in nodes if indeg[v] == 0]
+    done = 0
+    while ready:
+        g, j = ready.pop(rng.randrange(len(ready)))
+        done += 1
+        sl, ops, _ = slabs[g]
+        o, st, base = ops[j], state[g], sl.sub_lo
+        if o.kind == U:
+            st["staging"][o.lo:o.hi] = host_in[base + o.lo:base + o.hi]
+        elif o.kind == P:
+            st["g"][0][o.lo:o.hi] = st["staging"][o.lo:o.hi]
+            st["g"][1][o.lo:o.hi] = st["staging"][o.lo:o.hi]
+        elif o.kind == S:
+            _range_pass(st["g"][o.src], st["g"][o.src ^ 1], st["n"], r, shape, o.lo, o.hi, o.steps)
+        else:
+            host_dst[base + o.lo + r:base + o.hi + r][inner] = st["g"][o.src][o.lo + r:o.hi + r][inner]
+        for s in succ[(g, j)]:
+            indeg[s] -= 1
+            if indeg[s] == 0:
+                ready.append(s)
+    assert done == len(nodes)
+    assert not np.isnan(oracle.interior(host_dst, r)).any()
+    assert np.array_equal(host_dst.view(np.uint8), want.view(np.uint8))
+
+
+def _check_cross_slab_host_hazards(slabs, r, T):
+    """T even: downloads write the array uploads read.  Every (download of slab a, upload of slab
+    b) pair that touches the same host planes must be ordered by the zone rule."""
+    if T & 1:
+        return 0
+    found = 0
+    for a, (sla, opsa, _) in enumerate(slabs):
+        for b, (slb, opsb, zb) in enumerate(slabs):
+            if a == b:
+                continue
+            ups = [o for o in opsb if o.kind == U]
+            for d in (o for o in opsa if o.kind == D):
+                dlo, dhi = sla.sub_lo + d.lo + r, sla.sub_lo + d.hi + r
+                for q, u in enumerate(ups):
+                    if slb.sub_lo + u.lo < dhi and dlo < slb.sub_lo + u.hi:
+                        found += 1
+                        assert abs(a - b) == 1 and q < zb, "an unordered download/upload pair shares host planes"
+    return found
+
+
+SLAB_CASES = [
+    # n, r, shape, dtype, T, C, NS, G
+    ((12, 10, 96), 1, capi.STAR, capi.F64, 6, 4, 2, 3),     # T even: downloads land in the array others upload from
+    ((12, 10, 96), 1, capi.STAR, capi.F64, 7, 5, 2, 2),
+    ((9, 7, 128), 1, capi.BOX, capi.F32, 4, 3, 3, 4),
+    ((40, 260), 1, capi.BOX, capi.F32, 8, 4, 2, 4),         # WARP2D k=4, y-slabs
+    ((33, 200), 2, capi.STAR, capi.F64, 6, 5, 2, 2),        # radius 2: deep halo 12 rows
+    ((8, 6, 120), 2, capi.STAR, capi.F64, 5, 4, 1, 2),      # generic 3-D radius 2
+]
+
+
+@pytest.mark.parametrize("n,r,shape,dtype,T,C,NS,G", SLAB_CASES)
+def test_slab_schedules_race_free_and_exact(built, monkeypatch, n, r, shape, dtype, T, C, NS, G):
+    plan, slabs = _slab_setup(monkeypatch, n, r, shape, dtype, T, C, NS, G)
+    assert plan.ngpus_used == G and plan.deep_halo == T * r
+    assert slabs[0][0].own_lo == 0 and slabs[-1][0].own_hi == n[-1]
+    for g, (sl, ops, zones) in enumerate(slabs):
+        assert sl.sub_lo == max(0, sl.own_lo - T * r) and sl.sub_hi == min(n[-1], sl.own_hi + T * r)
+        if g:
+            assert sl.own_lo == slabs[g - 1][0].own_hi
+        _check_slab_structure(sl, ops, zones, r)
+        _check_race_free(ops, sl.sub_hi - sl.sub_lo, r, T)
+    if T % 2 == 0:
+        assert _check_cross_slab_host_hazards(slabs, r, T) > 0
+    rng = random.Random(99)
+    for _ in range(3):
+        _execute_slabs(plan, slabs, n, r, shape, dtype, T, rng)
+
+
+def test_slab_plan_uses_fewer_gpus_when_slabs_get_thin(built, monkeypatch):
+    monkeypatch.delenv("SB200_PIPELINE_CHUNKS", raising=False)
+    big = capi.make_desc((1024, 1024, 2048), dtype=capi.F64, iterations=40)       # config 5
+    p = capi.slab_plan(big, 8)
+    assert p.ngpus_used == 8 and p.slab[3].own_hi - p.slab[3].own_lo == 256
+    assert p.slab[3].sub_lo == p.slab[3].own_lo - 40 and p.slab[7].sub_hi == 2048
+    c2 = capi.make_desc((512, 512, 512), dtype=capi.F64, iterations=100)          # config 2
+    assert capi.slab_plan(c2, 8).ngpus_used == 2                                   # 256-plane slabs >= 2 * 100
+    assert capi.slab_plan(c2, 1).ngpus_used == 1
+    long_run = capi.make_desc((16384, 16384), shape=capi.BOX, iterations=1000)    # config 4
+    assert capi.slab_plan(long_run, 8).ngpus_used == 8                             # 2048 rows >= 2 * 1000
+    tiny = capi.make_desc((64, 64), iterations=1000)
+    assert capi.slab_plan(tiny, 8).ngpus_used == 1
+    assert capi.slab_plan(capi.make_desc((1 << 20,), iterations=4), 4).ngpus_used == 1   # 1-D never
