@@ -125,6 +125,8 @@ int sb200_init(int device);
 /* Bind the calling process to `n` devices at once (one process, N GPUs): the counterpart of
  * the reference's single Stencil::run driving the whole 64-CPE mesh from one host thread
  * (src/stencil/stencil.cpp:34-53; run.sh:3 `-cgsp 64`).  devices == NULL means 0..n-1.
+ * A device may be listed more than once: its slabs then share it, each with its own grids
+ * and streams (how the slab path is tested on a one-GPU box).
  * sb200_run_host then spreads a grid over them (sb200_desc.ngpus); the device-resident
  * calls keep operating on the first device of the group. */
 int sb200_init_multi(int n, const int* devices);

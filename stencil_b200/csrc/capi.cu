@@ -229,8 +229,6 @@ int bind_group(int n, const int* devices) {
     for (int i = 0; i < n; ++i) {
         const int d = devices ? devices[i] : i;
         if (d < 0 || d >= have) return fail(SB200_ERR_INVALID, "device %d of %d visible", d, have);
-        for (int j = 0; j < i; ++j)
-            if ((devices ? devices[j] : j) == d) return fail(SB200_ERR_INVALID, "device %d listed twice", d);
     }
     std::vector<State*> group;
     int rc = SB200_OK;

@@ -16,7 +16,8 @@
 struct ProgramOptions {
     /// Side length of the matrix.
     unsigned matrix_size = 0;
-    /// Reference: side of the tile each CPE owns. CUDA backend: tuning hint only.
+    /// Reference: side of the tile each CPE owns (program_options.hpp:11-13).  CUDA backend:
+    /// passed on as sb200_desc.block_hint, a tile / time-block preference.
     unsigned block_size = 0;
     /// Number of iterations.
     unsigned iterations = 0;
@@ -38,6 +39,7 @@ struct ProgramOptions {
     std::string init = "ref";     // ref | random
     unsigned long long seed = 1;
     std::string kernel = "auto";  // auto | generic | warp2d | tma3d | resident2d
+    unsigned gpus = 1;            // GPUs one CUDA run is spread over (slabs of the outermost axis)
     std::string json_path;        // append one JSON record per method here
     std::string bmp_path;         // write the final 2-D field as a BMP heat map
 

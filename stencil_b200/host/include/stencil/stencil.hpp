@@ -40,6 +40,8 @@ public:
         unsigned launches = 0, time_block = 0;
         int kernel = 0;
         int threads = 1;
+        unsigned gpus = 1;       // GPUs the run was spread over
+        bool pipelined = false;  // sweep_ms spans the whole overlapped upload/sweep/download pipeline
     };
 
     Stencil() = default;
@@ -62,6 +64,12 @@ public:
     double updates() const;  // interior points x iterations
 
     static bool parse_method(std::string_view name, InputMethod& out);
+
+    /// Untimed bring-up for the CUDA method (the counterpart of the reference's athread_init(),
+    /// src/main.cpp:54): device buffers, kernel attributes and one warm-up launch of every
+    /// kernel variant a run with these options takes.  Returns false (message in
+    /// sb200_last_error) if the backend is unusable; run() then reports the error.
+    static bool prepare_cuda(ProgramOptions const& options);
 
 private:
     template <class T> struct Pair {

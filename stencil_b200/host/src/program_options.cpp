@@ -35,6 +35,7 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
     app.option("--init", result.init, "Initial condition: ref or random.", std::string("ref"));
     app.option("--seed", result.seed, "Seed of the random initial condition.", 1ull);
     app.option("--kernel", result.kernel, "CUDA kernel family: auto, generic, warp2d, tma3d, resident2d, line1d.", std::string("auto"));
+    app.option("--gpus", result.gpus, "GPUs of this box one CUDA run is spread over (z-slabs; y-slabs in 2-D).", 1u);
     app.option("--json", result.json_path, "Append one JSON record per method to this file.");
     app.option("--bmp", result.bmp_path, "Write the final 2-D field as a BMP heat map.");
 
@@ -62,6 +63,7 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
         if (!one_of(result.init, {"ref", "random"})) throw cli::ParseError("--init must be ref or random", 105);
         if (!one_of(result.kernel, {"auto", "generic", "warp2d", "tma3d", "resident2d", "line1d"}))
             throw cli::ParseError("--kernel must be auto, generic, warp2d, tma3d, resident2d or line1d", 105);
+        if (result.gpus == 0 || result.gpus > 16) throw cli::ParseError("--gpus must be in 1..16", 105);
         if (result.radius == 0) throw cli::ParseError("--radius must be at least 1", 105);
         if (result.repeat_count == 0) throw cli::ParseError("--repeat must be at least 1", 105);
         if (result.shape.empty() && result.matrix_size == 0) throw cli::ParseError("--matrix-size must be positive", 105);

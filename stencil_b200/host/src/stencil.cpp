@@ -104,6 +104,7 @@ sb200_desc make_desc(ProgramOptions const& o) {
     d.iterations = o.iterations;
     d.time_block = o.time_block;
     d.block_hint = o.block_size;
+    d.ngpus = o.gpus;
     d.kernel = o.kernel == "generic" ? SB200_KERNEL_GENERIC
                : o.kernel == "warp2d" ? SB200_KERNEL_WARP2D
                : o.kernel == "tma3d"  ? SB200_KERNEL_TMA3D
@@ -126,6 +127,11 @@ bool Stencil::parse_method(std::string_view name, InputMethod& out) {
             return true;
         }
     return false;
+}
+
+bool Stencil::prepare_cuda(ProgramOptions const& options) {
+    sb200_desc const d = make_desc(options);
+    return sb200_prepare(&d) == SB200_OK;
 }
 
 template <class T>
@@ -181,6 +187,8 @@ auto Stencil::run_typed(InputMethod method) -> std::chrono::steady_clock::durati
         info_.launches = t.launches;
         info_.time_block = t.time_block;
         info_.kernel = t.kernel;
+        info_.gpus = t.ngpus;
+        info_.pipelined = t.pipelined != 0;
         break;
     }
     case CPU:

@@ -25,11 +25,11 @@ def padded_shape(n, r):
 
 
 def run_host(n, a: np.ndarray, b: np.ndarray, iterations: int, radius=1, shape=capi.STAR,
-             time_block=0, kernel=capi.KERNEL_AUTO):
+             time_block=0, kernel=capi.KERNEL_AUTO, ngpus=0, flags=0):
     """In-place on the two padded host arrays; returns (result_array, Timing)."""
     assert a.dtype == b.dtype and a.flags.c_contiguous and b.flags.c_contiguous
     assert a.shape == padded_shape(n, radius) == b.shape, (a.shape, padded_shape(n, radius))
-    d = capi.make_desc(n, radius, shape, dtype_code(a.dtype), iterations, time_block, 0, kernel)
+    d = capi.make_desc(n, radius, shape, dtype_code(a.dtype), iterations, time_block, 0, kernel, ngpus, flags)
     t = capi.Timing()
     capi.check(capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, b.ctypes.data,
                                          ctypes.byref(t)))
