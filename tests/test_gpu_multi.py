@@ -47,11 +47,12 @@ def _run(n, r, shape, dtype, T, ngpus, seed=1, time_block=0, kernel=capi.KERNEL_
     a = oracle.fill(n, r, code, oracle.INIT_RANDOM, seed)
     b = oracle.fill(n, r, code, oracle.INIT_REF)
     ga, gb = a.copy(), b.copy()
+    a0, b0 = a.copy(), b.copy()
     want = b if oracle.sweep(n, r, shape, T, a, b, threads=oracle.max_threads()) else a
     got, t = sweep.run_host(n, ga, gb, T, radius=r, shape=shape, time_block=time_block, kernel=kernel, ngpus=ngpus)
     assert np.array_equal(want.view(np.uint8), got.view(np.uint8)), \
         f"max|d|={np.abs(want.astype(np.float64) - got.astype(np.float64)).max()} gpus={t.ngpus}"
-    other, other0 = (ga, a) if T & 1 else (gb, b)
+    other, other0 = (ga, a0) if T & 1 else (gb, b0)
     assert np.array_equal(other.view(np.uint8), other0.view(np.uint8)), "the other buffer was touched"
     return t
 
