@@ -276,8 +276,13 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
                             const sb200_slab_link* link, void* stream, uint32_t* arrivals);
 
 /* Blocking read of the SB200_LINK_FLAG_WORDS flag words (after synchronising the
- * device): words[2] != 0 means a face CTA timed out waiting for a neighbour. */
+ * device): words[2] != 0 means a face CTA timed out (10 s) waiting for a neighbour; every
+ * result since is invalid.  The flag is sticky until sb200_link_reset. */
 int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLAG_WORDS]);
+/* Zero the flag words (arrival counters and the time-out flag).  Every rank of the chain must
+ * do it at the same quiescent point (device idle, barrier on both sides) and restart its
+ * wait_arrivals at 0. */
+int sb200_link_reset(uint32_t* flags_local);
 
 /* What the library WOULD do for `steps` steps of this descriptor on a whole grid of
  * a device with `sm_count` SMs — pure host logic, no device needed (tests, tuning,

@@ -28,7 +28,7 @@ SYMBOLS = [
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
     "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
     "sb200_init_multi", "sb200_group_size", "sb200_prepare", "sb200_slab_plan_for",
-    "sb200_pipeline_schedule_slab",
+    "sb200_pipeline_schedule_slab", "sb200_link_reset",
 ]
 MAX_GPUS = 16
 FLAG_REASSOCIATE = 1
@@ -151,6 +151,7 @@ def lib() -> ctypes.CDLL:
         L.sb200_ipc_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(vp)]
         L.sb200_ipc_close.argtypes = [vp]
         L.sb200_link_status.argtypes = [vp, ctypes.POINTER(u32)]
+        L.sb200_link_reset.argtypes = [vp]
         L.sb200_sweep_slab_linked.argtypes = [dp, u32, i32, i32, vp, vp, u32,
                                               ctypes.POINTER(SlabLink), vp, ctypes.POINTER(u32)]
         _lib = L

@@ -709,6 +709,14 @@ int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLA
     return SB200_OK;
 }
 
+int sb200_link_reset(uint32_t* flags_local) {
+    if (!flags_local) return fail(SB200_ERR_INVALID, "null argument");
+    CU_TRY(cudaDeviceSynchronize());
+    CU_TRY(cudaMemset(flags_local, 0, sizeof(uint32_t) * SB200_LINK_FLAG_WORDS));
+    CU_TRY(cudaDeviceSynchronize());
+    return SB200_OK;
+}
+
 int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
                             int hi_is_boundary, const void* a, void* b, uint32_t steps,
                             const sb200_slab_link* link, void* stream, uint32_t* arrivals) {

@@ -251,13 +251,13 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-// Bounded acquire-spin on an arrival counter: gives up after 2 s, and at once if another
+// Bounded acquire-spin on an arrival counter: gives up after 10 s, and at once if another
 // CTA already gave up — a broken link ends in a reported error (sb200_link_status), never
 // in a hung GPU.
 __device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsigned* err_flag) {
     const unsigned long long t0 = global_timer_ns();
     while ((int)(ld_acquire_sys_u32(flag) - want) < 0) {
-        if (global_timer_ns() - t0 > 2000000000ull || *(volatile unsigned*)err_flag != 0u) {
+        if (global_timer_ns() - t0 > 10000000000ull || *(volatile unsigned*)err_flag != 0u) {
             *(volatile unsigned*)err_flag = 1u;
             break;
         }

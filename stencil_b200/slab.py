@@ -161,6 +161,11 @@ class CudaEngine:
         self.arrivals += arr.value
         return 1
 
+    def link_reset(self) -> None:
+        """Zero the arrival counters and the time-out flag (all ranks, at a quiescent point)."""
+        capi.check(capi.lib().sb200_link_reset(self.flags.data_ptr()))
+        self.arrivals = 0
+
     def link_timed_out(self) -> bool:
         """True if any face CTA gave up waiting for a neighbour (results are then invalid)."""
         words = (ctypes.c_uint32 * capi.LINK_FLAG_WORDS)()
@@ -294,15 +299,31 @@ class SlabSweep:
         if self.world == 1:
             off = tot = 0
         self._quiesce()
+        if self.exchange == "p2p":
+            # a time-out of an earlier run must not poison this one: counters restart at 0 on
+            # every rank between the two barriers of the quiesce
+            self.check_link()
+            self.eng.link_reset()
+            self.dist.barrier()
         self.eng.fill(0, init, seed, off, tot)
         self.eng.fill(1, capi.INIT_REF, 0, off, tot)
         self.cur = 0
         self._quiesce()
 
+    def check_link(self) -> None:
+        """p2p: raise if a face CTA ever gave up waiting for its neighbour (the ghost planes it
+        then read were stale, so every result since is invalid).  Synchronises the device.
+        Called at every host sync point of this class; callers that time a region call it
+        right after the region."""
+        if self.exchange == "p2p" and self.eng is not None and self.eng.link_timed_out():
+            raise RuntimeError(f"rank {self.rank}: a fused halo exchange timed out waiting for a neighbour; "
+                               "results are invalid")
+
     def close(self):
         """p2p: unmap the neighbours' memory on every rank BEFORE any rank frees its grids."""
         if self.exchange == "p2p" and self.eng is not None:
             self._quiesce()
+            self.check_link()
             self.eng.close_peers()
             self.dist.barrier()
             self.eng.free()
@@ -312,6 +333,7 @@ class SlabSweep:
         off, tot = self.rank * self.n_outer, self.n_outer * self.world
         if self.world == 1:
             off = tot = 0
+        self.check_link()
         return self.eng.checksum(self.cur, off, tot)
 
     def download_initial_into(self, ha, hb, seed):

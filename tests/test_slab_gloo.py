@@ -89,6 +89,12 @@ class OracleEngine:
     def sync(self):
         pass
 
+    def link_reset(self):
+        self.resets = getattr(self, "resets", 0) + 1
+
+    def link_timed_out(self):
+        return False
+
     def sweep_linked(self, src, dst, steps, lo_b, hi_b):
         n, g = self.n[-1], self.ghost
         self.sweep_range(src, dst, steps, 0, n, lo_b, hi_b)
