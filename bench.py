@@ -187,7 +187,7 @@ def run_reference(args):
                          "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "parity": PARITY,
-    }))
+    }), flush=True)
 
 
 # ---- BASELINE configs[4]: 2048 x 1024 x 1024 fp64, strong scaling -----------------------------
@@ -474,7 +474,7 @@ def main():
                          "value": c5["value"], "scaling": "strong", "ms_per_step": c5["ms_per_sweep"],
                          "config": {"workload": c5["workload"], "grid": [C5_NXY, C5_NXY, C5_NZ], "time_steps": C5_T,
                                     "parallelism": f"z-slab x{world}"}, "headline_config2": value})
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)   # flushed here: a teardown hiccup must not eat the line
     if world > 1:
         dist.destroy_process_group()
 
