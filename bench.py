@@ -316,15 +316,17 @@ def e2e_leg(args, torch, dist, capi, rank, world, local, cpu_barrier):
     capi.check(L.sb200_init_multi(world, None))
     hp = [ctypes.c_void_p(), ctypes.c_void_p()]
     host = []
+    desc = capi.make_desc((N_SIDE, N_SIDE, nz), 1, capi.STAR, capi.F64, T_STEPS, time_block=args.time_block, ngpus=world)
+    nodes = ctypes.c_int(0)
     for p, blk in zip(hp, blocks):
-        capi.check(L.sb200_host_alloc(ctypes.byref(p), nbytes))
+        # page-locked, every slab's planes on the memory node of its GPU
+        capi.check(L.sb200_host_alloc_for(ctypes.byref(desc), ctypes.byref(p), ctypes.byref(nodes)))
         h = np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(ctypes.c_double)), shape=shape)
         h[0] = blk[0]
         for b in range(world):
             h[1 + b * N_SIDE:1 + (b + 1) * N_SIDE] = blk[1:-1]
         h[-1] = blk[-1]
         host.append(h)
-    desc = capi.make_desc((N_SIDE, N_SIDE, nz), 1, capi.STAR, capi.F64, T_STEPS, time_block=args.time_block, ngpus=world)
     capi.check(L.sb200_prepare(ctypes.byref(desc)))
     tm = capi.Timing()
     capi.check(L.sb200_run_host(ctypes.byref(desc), hp[0], hp[1], ctypes.byref(tm)))   # warm
@@ -337,7 +339,7 @@ def e2e_leg(args, torch, dist, capi, rank, world, local, cpu_barrier):
     up_planes = sum(plan.slab[i].sub_hi - plan.slab[i].sub_lo + 2 for i in range(plan.ngpus_used))
     e2e = {"value": N_SIDE ** 3 * world * T_STEPS * e2e_steps / dt / 1e9, "unit": UNIT,
            "h2d_bytes_per_step": int(up_planes) * shape[1] * shape[2] * 8, "d2h_bytes_per_step": N_SIDE ** 3 * world * 8,
-           "steps": e2e_steps, "ms_per_call": dt / e2e_steps * 1e3,
+           "steps": e2e_steps, "ms_per_call": dt / e2e_steps * 1e3, "host_memory_nodes": nodes.value,
            "h2d_ms": tm.h2d_ms, "sweep_ms": tm.sweep_ms, "d2h_ms": tm.d2h_ms, "gpus_used": tm.ngpus,
            "grid": [N_SIDE, N_SIDE, nz],
            "note": "ONE sb200_run_host call from one process on pinned host buffers holding the whole "

@@ -231,6 +231,15 @@ int sb200_host_free(void* ptr);
  * by the driver and cannot overlap with the sweep.  Costs ~0.1 ms per MB once. */
 int sb200_host_register(void* ptr, size_t bytes);
 int sb200_host_unregister(void* ptr);
+/* NUMA placement for multi-GPU calls: the planes slab g owns are put on the memory node GPU g
+ * hangs off (PCIe root of its socket), so that no upload or download crosses the socket
+ * interconnect.  sb200_host_alloc_for returns page-locked memory for one dense grid of `desc`
+ * placed that way (free it with sb200_host_free); sb200_host_place MOVES the pages of a
+ * caller-owned grid (call it before sb200_host_register).  Both are hints: on a single-node
+ * host, or where the kernel refuses (containers without CAP_SYS_NICE), they change nothing and
+ * still succeed.  *nodes_used (may be NULL) = number of distinct memory nodes chosen. */
+int sb200_host_alloc_for(const sb200_desc* desc, void** ptr, int* nodes_used);
+int sb200_host_place(const sb200_desc* desc, void* ptr, int* nodes_used);
 
 /* ---- multi-GPU slab link: halo exchange fused into the sweep kernel ------------
  * One process per GPU.  Replaces the reference's on-chip RMA halo puts + reply

@@ -28,7 +28,7 @@ SYMBOLS = [
     "sb200_ipc_close", "sb200_sweep_slab_linked", "sb200_link_status",
     "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
     "sb200_init_multi", "sb200_group_size", "sb200_prepare", "sb200_slab_plan_for",
-    "sb200_pipeline_schedule_slab", "sb200_link_reset",
+    "sb200_pipeline_schedule_slab", "sb200_link_reset", "sb200_host_alloc_for", "sb200_host_place",
 ]
 MAX_GPUS = 16
 FLAG_REASSOCIATE = 1
@@ -140,6 +140,8 @@ def lib() -> ctypes.CDLL:
         L.sb200_checksum_device.argtypes = [dp, u32, vp, u64, u64, vp, ctypes.POINTER(u64)]
         L.sb200_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_host_free.argtypes = [vp]
+        L.sb200_host_alloc_for.argtypes = [dp, ctypes.POINTER(vp), ctypes.POINTER(i32)]
+        L.sb200_host_place.argtypes = [dp, vp, ctypes.POINTER(i32)]
         L.sb200_host_register.argtypes = [vp, ctypes.c_size_t]
         L.sb200_host_unregister.argtypes = [vp]
         L.sb200_plan.argtypes = [dp, u32, i32, ctypes.POINTER(PlanInfo)]

@@ -5,6 +5,9 @@
 // entry point fails with SB200_ERR_NO_DEVICE when no CUDA device is usable.
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <sys/mman.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 
 #include <chrono>
 #include <cstdarg>
@@ -1265,10 +1268,111 @@ int sb200_host_alloc(void** ptr, size_t bytes) {
     return SB200_OK;
 }
 
+// ---- NUMA placement of host grids (no libnuma on the image: raw mbind) ----------------------
+static int gpu_numa_node(int dev) {
+    char bus[32];
+    if (cudaDeviceGetPCIBusId(bus, sizeof bus, dev) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    for (char* p = bus; *p; ++p) *p = (char)tolower((unsigned char)*p);
+    char path[96];
+    snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+    FILE* f = fopen(path, "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
+
+// Prefer memory node `node` for the pages inside [p, p + bytes) (rounded inwards to pages);
+// move == true also migrates pages that already exist.
+static bool prefer_node(char* p, size_t bytes, int node, bool move) {
+    const uintptr_t page = (uintptr_t)sysconf(_SC_PAGESIZE);
+    const uintptr_t lo = ((uintptr_t)p + page - 1) / page * page, hi = ((uintptr_t)p + bytes) / page * page;
+    if (node < 0 || node >= 1024 || hi <= lo) return false;
+    unsigned long mask[16] = {0};
+    mask[node / 64] = 1ul << (node % 64);
+    return syscall(SYS_mbind, (void*)lo, (size_t)(hi - lo), 1 /* MPOL_PREFERRED */, mask, 1024ul,
+                   move ? 2u /* MPOL_MF_MOVE */ : 0u) == 0;
+}
+
+static size_t dense_host_bytes(const sb200_desc* d) {
+    size_t b = esize(d->dtype);
+    for (int a = 0; a < d->ndim; ++a) b *= (size_t)(d->n[a] + 2 * d->radius);
+    return b;
+}
+
+// Put the planes each slab owns on its GPU's memory node.  Returns the number of distinct nodes.
+static int place_slabs(const sb200_desc* d, char* base, bool move) {
+    const int have = (int)g_group.size();
+    const int want = d->ngpus == 0 ? have : (int)d->ngpus < have ? (int)d->ngpus : have;
+    sb200_slab_plan plan;
+    if (want < 2 || slab_plan_impl(d, want, &plan) != SB200_OK || plan.ngpus_used < 2) return 0;
+    const size_t outer_bytes = dense_host_bytes(d) / (size_t)(d->n[d->ndim - 1] + 2 * d->radius);
+    int nodes[SB200_MAX_GPUS], distinct = 0;
+    for (uint32_t i = 0; i < plan.ngpus_used; ++i) {
+        nodes[i] = gpu_numa_node(g_group[i]->device);
+        // padded index = interior index + radius; the end slabs take the halo planes along
+        const size_t lo = i == 0 ? 0 : (size_t)(plan.slab[i].own_lo + d->radius) * outer_bytes;
+        const size_t hi = i + 1 == plan.ngpus_used ? dense_host_bytes(d) : (size_t)(plan.slab[i].own_hi + d->radius) * outer_bytes;
+        if (!prefer_node(base + lo, hi - lo, nodes[i], move)) continue;
+        bool seen = false;
+        for (uint32_t j = 0; j < i; ++j) seen = seen || nodes[j] == nodes[i];
+        distinct += !seen;
+    }
+    return distinct;
+}
+
+struct PlacedAlloc {
+    void* ptr;
+    size_t bytes;
+};
+static std::vector<PlacedAlloc> g_placed;  // sb200_host_alloc_for allocations (mmap + register)
+
+int sb200_host_alloc_for(const sb200_desc* desc, void** ptr, int* nodes_used) {
+    if (int rc = validate(desc)) return rc;
+    if (!ptr) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    const size_t bytes = dense_host_bytes(desc);
+    void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (p == MAP_FAILED) return fail(SB200_ERR_INVALID, "mmap of %zu bytes failed", bytes);
+    const int nodes = place_slabs(desc, (char*)p, false);  // policy first, pages appear at registration
+    if (cudaHostRegister(p, bytes, cudaHostRegisterPortable) != cudaSuccess) {
+        const cudaError_t e = cudaGetLastError();
+        munmap(p, bytes);
+        return fail(SB200_ERR_CUDA, "cudaHostRegister of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+    }
+    g_placed.push_back({p, bytes});
+    *ptr = p;
+    if (nodes_used) *nodes_used = nodes;
+    return SB200_OK;
+}
+
+int sb200_host_place(const sb200_desc* desc, void* ptr, int* nodes_used) {
+    if (int rc = validate(desc)) return rc;
+    if (!ptr) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    const int nodes = place_slabs(desc, (char*)ptr, true);
+    if (nodes_used) *nodes_used = nodes;
+    return SB200_OK;
+}
+
 int sb200_host_free(void* ptr) {
     if (!ptr) return SB200_OK;
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
+    for (size_t i = 0; i < g_placed.size(); ++i)
+        if (g_placed[i].ptr == ptr) {
+            const size_t bytes = g_placed[i].bytes;
+            g_placed.erase(g_placed.begin() + (long)i);
+            CU_TRY(cudaHostUnregister(ptr));
+            munmap(ptr, bytes);
+            return SB200_OK;
+        }
     CU_TRY(cudaFreeHost(ptr));
     return SB200_OK;
 }

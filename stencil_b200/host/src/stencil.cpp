@@ -162,6 +162,12 @@ auto Stencil::run_typed(InputMethod method) -> std::chrono::steady_clock::durati
     // the sweep.  Small grids are not worth the registration cost.
     std::size_t const bytes = p.matrix.width_with_boundary() * p.matrix.height_with_boundary() *
                               p.matrix.depth_with_boundary() * sizeof(T);
+    if (method == CUDA && options.gpus > 1 && bytes >= (std::size_t(64) << 20)) {
+        // every slab's planes onto the memory node of the GPU that sweeps them (a hint)
+        sb200_desc const d = make_desc(options);
+        (void)sb200_host_place(&d, p.matrix.raw_data(), nullptr);
+        (void)sb200_host_place(&d, p.result.raw_data(), nullptr);
+    }
     bool const pin = method == CUDA && bytes >= (std::size_t(64) << 20) &&
                      sb200_host_register(p.matrix.raw_data(), bytes) == SB200_OK;
     bool const pin2 = pin && sb200_host_register(p.result.raw_data(), bytes) == SB200_OK;
