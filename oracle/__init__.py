@@ -77,6 +77,9 @@ def ref_lib():
         R.ref_check_2d_f32.argtypes = [ctypes.c_uint] * 3 + [ctypes.c_void_p]
         R.ref_time_check_2d_f32.restype = ctypes.c_double
         R.ref_time_check_2d_f32.argtypes = [ctypes.c_uint] * 3
+        if hasattr(R, "ref_bmp_2d_f32"):
+            R.ref_bmp_2d_f32.restype = ctypes.c_int
+            R.ref_bmp_2d_f32.argtypes = [ctypes.c_uint, ctypes.c_void_p, ctypes.c_char_p]
         _ref = R
     return _ref
 
@@ -139,6 +142,17 @@ def ref_naive_2d_f32(N: int, r: int, T: int) -> np.ndarray:
     if R.ref_naive_2d_f32(N, r, T, out.ctypes.data) != 0:
         raise RuntimeError("reference probe protocol failed")
     return out
+
+
+def ref_bmp_2d_f32(grid: np.ndarray, path: str) -> None:
+    """The GENUINE reference heat-map writer (Stencil::to_bmp + BMPImage::save) on `grid`."""
+    R = ref_lib()
+    if R is None:
+        raise RuntimeError("oracle/_ref/libref.so not built (needs /root/reference)")
+    g = np.ascontiguousarray(grid, dtype=np.float32)
+    assert g.ndim == 2 and g.shape[0] == g.shape[1]
+    if R.ref_bmp_2d_f32(g.shape[0], g.ctypes.data, path.encode()) != 0:
+        raise RuntimeError("reference BMP writer failed")
 
 
 _ref64 = None

@@ -101,6 +101,22 @@ int ref_check_2d_f32(unsigned N, unsigned r, unsigned T, const float* grid) {
     return s.check_result() ? 1 : 0;
 }
 
+// The reference's own heat-map writer (Stencil::to_bmp + BMPImage::save, stencil.cpp:153-188,
+// bmp_image.cpp:7-64) on a planted field: pins the on-disk format of --bmp.
+int ref_bmp_2d_f32(unsigned N, const float* grid, const char* path) {
+    ProgramOptions opts{};
+    opts.matrix_size = N;
+    opts.block_size = N;
+    opts.iterations = 0;
+    opts.radius = 1;
+    Stencil s(opts);
+    s.initialize_matrix();
+    for (unsigned row = 0; row != N; ++row)
+        for (unsigned col = 0; col != N; ++col) s.matrix.elem_at(row, col) = grid[row * N + col];
+    s.to_bmp().save(path);
+    return 0;
+}
+
 // Time the reference's own naive loop (whole check_result: init + sweep + compare), for
 // the "reference"-kind CPU baseline. Returns seconds.
 double ref_time_check_2d_f32(unsigned N, unsigned r, unsigned T) {

@@ -15,7 +15,8 @@ public:
     };
     BMPImage(std::vector<Pixel> pixels, unsigned width, unsigned height)
         : pixels_(std::move(pixels)), width_(width), height_(height) {}
-    /// Rows are stored top-down in `pixels`; returns false if the file cannot be written.
+    /// Rows are written in the order they are stored (the reference's on-disk format,
+    /// src/stencil/bmp_image.cpp:19-25); returns false if the file cannot be written.
     bool save(std::string const& path) const;
     unsigned width() const { return width_; }
     unsigned height() const { return height_; }

@@ -22,13 +22,12 @@ bool BMPImage::save(std::string const& path) const {
     put_le(f, height_, 4);
     put_le(f, 1, 2);
     put_le(f, 24, 2);
-    put_le(f, 0, 4);
-    put_le(f, data_bytes, 4);
-    put_le(f, 2835, 4);
-    put_le(f, 2835, 4);
-    put_le(f, 0, 4);
-    put_le(f, 0, 4);
-    for (unsigned y = height_; y-- > 0;) {  // BMP rows are bottom-up
+    // the rest of the info header stays zero and rows go out in storage order (grid row 0
+    // first, which BMP viewers show at the bottom): byte for byte the file the reference's
+    // writer produces (src/stencil/bmp_image.cpp:7-64)
+    (void)data_bytes;
+    for (int i = 0; i < 6; ++i) put_le(f, 0, 4);
+    for (unsigned y = 0; y < height_; ++y) {
         for (unsigned x = 0; x < width_; ++x) {
             Pixel const& p = pixels_[static_cast<std::size_t>(y) * width_ + x];
             f.put(static_cast<char>(p.b)).put(static_cast<char>(p.g)).put(static_cast<char>(p.r));

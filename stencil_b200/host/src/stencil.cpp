@@ -258,31 +258,44 @@ auto Stencil::check_result() const -> bool {
 }
 
 auto Stencil::to_bmp() const -> BMPImage {
-    // Blue -> cyan -> green -> yellow -> red heat map of the FINAL field (the reference's
-    // to_bmp reads `matrix` regardless of parity, stencil.cpp:159; fixed here).
+    // Blue -> cyan -> green -> yellow -> red heat map of the FINAL field, with the reference's
+    // own colour arithmetic (stencil.cpp:153-188: the first ramp in the element type, the others
+    // in double, truncating conversions) so that the file is byte-identical to the reference's
+    // for the same field.  The reference reads `matrix` regardless of parity (stencil.cpp:159);
+    // here the buffer that holds step T is read.  Values outside [0, 1] are clamped.
     unsigned const w = options.extent(0), h = options.extent(1);
     std::vector<BMPImage::Pixel> px;
     px.reserve(std::size_t(w) * h);
     bool const in_result = options.iterations & 1u;
-    auto value_at = [&](std::size_t row, std::size_t col) -> double {
-        return std::visit([&](auto const& p) { return double((in_result ? p.result : p.matrix).elem_at(0, row, col)); },
-                          grids);
-    };
-    auto ramp = [](double v) { return static_cast<unsigned char>(std::fmin(std::fmax(v, 0.0), 1.0) * 255.0); };
-    for (unsigned row = 0; row < h; ++row)
-        for (unsigned col = 0; col < w; ++col) {
-            double const v = std::fmin(std::fmax(value_at(row, col), 0.0), 1.0);
-            BMPImage::Pixel p;
-            if (v < 0.25) {
-                p.g = ramp(4 * v), p.b = 255;
-            } else if (v < 0.5) {
-                p.g = 255, p.b = ramp(1 + 4 * (0.25 - v));
-            } else if (v < 0.75) {
-                p.r = ramp(4 * (v - 0.5)), p.g = 255;
-            } else {
-                p.r = 255, p.g = ramp(1 + 4 * (0.75 - v));
-            }
-            px.push_back(p);
-        }
+    std::visit(
+        [&](auto const& p) {
+            using T = std::decay_t<decltype(p.matrix.elem_at(0, 0, 0))>;
+            auto const& m = in_result ? p.result : p.matrix;
+            for (unsigned row = 0; row < h; ++row)
+                for (unsigned col = 0; col < w; ++col) {
+                    T value = m.elem_at(0, row, col);
+                    value = value < T(0) ? T(0) : value > T(1) ? T(1) : value;
+                    BMPImage::Pixel rgb;
+                    if (value < 0.25) {
+                        rgb.r = 0;
+                        rgb.g = static_cast<unsigned char>(4 * value * 255);
+                        rgb.b = 255;
+                    } else if (value < 0.5) {
+                        rgb.r = 0;
+                        rgb.g = 255;
+                        rgb.b = static_cast<unsigned char>((1 + 4 * (0.25 - value)) * 255);
+                    } else if (value < 0.75) {
+                        rgb.r = static_cast<unsigned char>((4 * (value - 0.5)) * 255);
+                        rgb.g = 255;
+                        rgb.b = 0;
+                    } else {
+                        rgb.r = 255;
+                        rgb.g = static_cast<unsigned char>((1 + 4 * (0.75 - value)) * 255);
+                        rgb.b = 0;
+                    }
+                    px.push_back(rgb);
+                }
+        },
+        grids);
     return BMPImage(std::move(px), w, h);
 }

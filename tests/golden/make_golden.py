@@ -42,6 +42,11 @@ CASES_EMU = [
 
 if __name__ == "__main__":
     oracle.build()
+    # the reference's own BMP writer on its own result (N=20, T=30: even, so the field is in
+    # `matrix`, the buffer the reference's to_bmp reads, stencil.cpp:159): pins --bmp
+    bmp = os.path.join(os.path.dirname(__file__), "ref_bmp_N20_T30.bmp")
+    oracle.ref_bmp_2d_f32(oracle.ref_naive_2d_f32(20, 1, 30), bmp)
+    print("bmp", os.path.getsize(bmp), "bytes")
     out = {}
     for N, r, T in CASES:
         out[f"N{N}_r{r}_T{T}"] = oracle.ref_naive_2d_f32(N, r, T)

@@ -66,6 +66,10 @@ def test_bmp_dump(built, tmp_path):
     assert r.returncode == 0
     data = p.read_bytes()
     assert data[:2] == b"BM" and len(data) == 54 + 20 * 60
+    # byte-identical to the file the reference's own Stencil::to_bmp + BMPImage::save write for
+    # the same field (tests/golden/make_golden.py drives them through oracle/_ref/libref.so)
+    gold = open(os.path.join(ROOT, "tests", "golden", "ref_bmp_N20_T30.bmp"), "rb").read()
+    assert data == gold
 
 
 @pytest.mark.gpu

@@ -100,11 +100,15 @@ def test_ref_init_layout():
 
 @pytest.mark.parametrize("dtype", [oracle.F32, oracle.F64])
 @pytest.mark.parametrize("shape", [oracle.STAR, oracle.BOX])
-@pytest.mark.parametrize("n", [(17,), (6, 5), (5, 4, 3)])
-def test_oracle_matches_numpy_restatement(n, shape, dtype):
-    """Independent numpy restatement (same add order) for every ndim/shape/dtype."""
-    r, T = 1, 3
-    a = oracle.fill(n, r, dtype, oracle.INIT_RANDOM, seed=11)
+@pytest.mark.parametrize("init", [oracle.INIT_RANDOM, oracle.INIT_REF])
+@pytest.mark.parametrize("n,r", [((17,), 1), ((6, 5), 1), ((5, 4, 3), 1), ((23,), 3), ((11, 9), 2), ((9, 12), 4),
+                                 ((7, 6, 5), 2), ((9, 8, 7), 3)])
+def test_oracle_matches_numpy_restatement(n, r, init, shape, dtype):
+    """Independent numpy restatement (same add order) for every ndim / shape / dtype, radius
+    1..4, and both initial conditions — the reference one puts 1 on the x faces over the full
+    padded extent of the other axes, so box corners see it."""
+    T = 3
+    a = oracle.fill(n, r, dtype, init, seed=11)
     b = oracle.fill(n, r, dtype, oracle.INIT_REF)
     x, y = a.copy(), b.copy()
     nd = len(n)
@@ -119,16 +123,17 @@ def test_oracle_matches_numpy_restatement(n, shape, dtype):
         if shape == oracle.STAR:
             for ax in range(nd):               # x first = last numpy axis
                 npax = nd - 1 - ax
-                for k in (-1, 1):
+                # low side far -> near, then high side near -> far (stencil.cpp:103-123)
+                for k in list(range(-r, 0)) + list(range(1, r + 1)):
                     off = [0] * nd
                     off[npax] = k
                     s = (s + sh(x, off)).astype(dt)
             avg = dt(1) / dt(2 * nd * r)
         else:
             import itertools
-            for off in itertools.product(*[(-1, 0, 1)] * nd):   # z outer ... x inner
+            for off in itertools.product(*[range(-r, r + 1)] * nd):   # z outer ... x inner, ascending
                 s = (s + sh(x, off)).astype(dt)
-            avg = dt(1) / dt(3 ** nd)
+            avg = dt(1) / dt((2 * r + 1) ** nd)
         y[inner] = s * avg
         x, y = y, x
     want = b if oracle.sweep(n, r, shape, T, a, b) else a
