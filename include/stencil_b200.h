@@ -79,7 +79,12 @@ typedef enum sb200_flags {
     /* Allow kernels that re-associate the sum of a point (separable box sums): results
      * then agree with the reference order within the north-star tolerance (max relative
      * error 1e-12 fp64 / 1e-5 fp32) instead of bit for bit.  Off by default. */
-    SB200_FLAG_REASSOCIATE = 1
+    SB200_FLAG_REASSOCIATE = 1,
+    /* Read block_hint (the reference's -b/--block-size: the side of the tile one CPE owns) as
+     * this backend's tile preference: the number of rows (2-D) / planes (3-D) of the outermost
+     * axis one warp (WARP2D) or CTA (TMA3D) streams, instead of the planner's own choice.
+     * sb200_plan reports the resulting geometry.  Other kernel families ignore it. */
+    SB200_FLAG_BLOCK_TILE = 2
 } sb200_flags;
 
 /* Timing breakdown of one call (milliseconds; device times from CUDA events).

@@ -25,13 +25,22 @@ def main():
     ap.add_argument("--out", default="output.csv")
     ap.add_argument("--blocks", nargs="+", type=int, default=block_sizes)
     ap.add_argument("--iters", nargs="+", type=int, default=iterations)
+    ap.add_argument("--size", type=int, default=0,
+                    help="fixed matrix size (default: 8 * block, as in the reference's sweep, run_expr.py:14)")
+    ap.add_argument("--block-as-tile", action="store_true",
+                    help="CUDA reads -b as its tile preference (rows per warp), so the block column of the CSV "
+                         "is a real tuning axis on this backend too; combine with --size to sweep it at a fixed N")
+    ap.add_argument("--extra", nargs=argparse.REMAINDER, default=[], help="further stencil_main flags")
     args = ap.parse_args()
     outputs = []
     for block_size in args.blocks:
         for iteration in args.iters:
-            matrix_size = block_size * 8
+            matrix_size = args.size or block_size * 8
             command = [BIN, '-s', str(matrix_size), '-b', str(block_size), '-i', str(iteration),
                        '-R', str(args.repeat), '-m', *args.methods]
+            if args.block_as_tile:
+                command.append('--block-as-tile')
+            command += args.extra
             print(f'----------- block size: {block_size}, iteration: {iteration} -----------')
             result = subprocess.run(command, capture_output=True, text=True)
             output = result.stdout.strip()

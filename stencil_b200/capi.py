@@ -32,6 +32,7 @@ SYMBOLS = [
 ]
 MAX_GPUS = 16
 FLAG_REASSOCIATE = 1
+FLAG_BLOCK_TILE = 2
 PIPE_UPLOAD, PIPE_UNPACK, PIPE_SWEEP, PIPE_DOWNLOAD = 0, 1, 2, 3
 IPC_HANDLE_BYTES = 64
 LINK_FLAG_WORDS = 4

@@ -131,7 +131,7 @@ int validate(const sb200_desc* d) {
     if (d->kernel < SB200_KERNEL_AUTO || d->kernel > SB200_KERNEL_LINE1D)
         return fail(SB200_ERR_INVALID, "bad kernel selector %d", d->kernel);
     if (d->ngpus > SB200_MAX_GPUS) return fail(SB200_ERR_INVALID, "ngpus must be 0..%d (got %u)", SB200_MAX_GPUS, d->ngpus);
-    if (d->flags & ~(uint32_t)SB200_FLAG_REASSOCIATE) return fail(SB200_ERR_INVALID, "unknown flag bits 0x%x", d->flags);
+    if (d->flags & ~(uint32_t)(SB200_FLAG_REASSOCIATE | SB200_FLAG_BLOCK_TILE)) return fail(SB200_ERR_INVALID, "unknown flag bits 0x%x", d->flags);
     return SB200_OK;
 }
 
@@ -297,7 +297,7 @@ int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap*
 
 template <class T, int K, int SHAPE>
 int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, long long ob,
-                   long long oe, cudaStream_t st, const SlabLinkDev& link_in) {
+                   long long oe, cudaStream_t st, const SlabLinkDev& link_in, int prefer_chunk) {
     using C = T3<T, K>;
     if (oe <= ob) return SB200_OK;
     const bool linked = link_in.link_lo || link_in.link_hi;
@@ -306,7 +306,7 @@ int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, lo
         return rc;
     const CUtensorMap* map = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, &map)) return rc;
-    const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, DS().sm_count);
+    const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
     const T avg = Avg<T>::value(SHAPE, 3, 1);
     if (linked) {
         SlabLinkDev link = link_in;
@@ -328,18 +328,19 @@ const SlabLinkDev kNoLink = {};
 
 template <class T>
 int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domain dom, int K,
-                 long long ob, long long oe, cudaStream_t st, const SlabLinkDev& link = kNoLink) {
+                 long long ob, long long oe, cudaStream_t st, const SlabLinkDev& link = kNoLink,
+                 int prefer_chunk = 0) {
     if (shape == SB200_BOX) {
         switch (K) {
-            case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st, link);
-            case 2: return launch_tma3d_k<T, 2, BOX>(in, out, dtype, g, dom, ob, oe, st, link);
+            case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
+            case 2: return launch_tma3d_k<T, 2, BOX>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
             default: return fail(SB200_ERR_INVALID, "TMA3D box time block %d out of range", K);
         }
     }
     switch (K) {
-        case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
-        case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
-        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st, link);
+        case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
+        case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
+        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
         default: return fail(SB200_ERR_INVALID, "TMA3D time block %d out of range", K);
     }
 }
@@ -391,6 +392,11 @@ int check_choice(const sb200_desc* d, const Choice& c) {
     return SB200_OK;
 }
 
+// -b/--block-size as a tile preference (opt-in): rows / planes one CTA or warp streams.
+int tile_pref(const sb200_desc* d) {
+    return (d->flags & SB200_FLAG_BLOCK_TILE) && d->block_hint > 0 ? (int)(d->block_hint > (1u << 20) ? (1u << 20) : d->block_hint) : 0;
+}
+
 // One fused pass of k steps: a -> b over outermost range [ob, oe).
 template <class T>
 int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, const T* a, T* b, int k,
@@ -402,12 +408,12 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_WARP2D:
             if (g.r > 1)
-                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, DS().sm_count, st));
+                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             else
-                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, DS().sm_count, st));
+                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
-            return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st);
+            return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st, kNoLink, tile_pref(d));
         case SB200_KERNEL_LINE1D:
             CU_TRY(launch_line1d<T>(a, b, g, d->shape, k, st));
             return SB200_OK;
@@ -582,7 +588,7 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     info->launches = (steps + c.k - 1) / c.k;
     const int k = steps && steps < (uint32_t)c.k ? (int)steps : c.k;
     if (c.kernel == SB200_KERNEL_WARP2D) {
-        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r);
+        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r, tile_pref(desc));
         info->tiles_x = (uint32_t)p.nstrips;
         info->tiles_y = 1;
         info->chunks = (uint32_t)p.nchunks;
@@ -590,13 +596,13 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     } else if (c.kernel == SB200_KERNEL_TMA3D) {
         T3Plan p;
         if (desc->dtype == SB200_F64)
-            p = k == 1 ? t3_plan<double, 1>(g.n[0], g.n[1], g.n[2], sm_count)
-                : k == 2 ? t3_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count)
-                         : t3_plan<double, 3>(g.n[0], g.n[1], g.n[2], sm_count);
+            p = k == 1 ? t3_plan<double, 1>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                : k == 2 ? t3_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                         : t3_plan<double, 3>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
         else
-            p = k == 1 ? t3_plan<float, 1>(g.n[0], g.n[1], g.n[2], sm_count)
-                : k == 2 ? t3_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count)
-                         : t3_plan<float, 3>(g.n[0], g.n[1], g.n[2], sm_count);
+            p = k == 1 ? t3_plan<float, 1>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                : k == 2 ? t3_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                         : t3_plan<float, 3>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
         info->tiles_x = (uint32_t)p.ntx;
         info->tiles_y = (uint32_t)p.nty;
         info->chunks = (uint32_t)p.nchunks;

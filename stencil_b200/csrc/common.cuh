@@ -39,6 +39,15 @@ struct Domain {
     long long lo, hi;
 };
 
+// What the planners need to know about the device and the caller's preferences.
+// prefer_chunk > 0: rows / planes of the outermost axis one CTA (tma3d) or warp (warp2d) should
+// stream — the reference's -b/--block-size (the side of the tile one CPE owns,
+// program_options.cpp:16-18) reinterpreted for this backend (SB200_FLAG_BLOCK_TILE).
+struct Tuning {
+    int sm_count;
+    int prefer_chunk;
+};
+
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;

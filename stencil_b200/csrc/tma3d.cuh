@@ -529,12 +529,18 @@ struct T3Plan {
 // dispatched in blockIdx order to the first free SM (1 CTA per SM): pick the chunk count
 // with the smallest simulated makespan (in plane-steps).
 template <class T, int K>
-static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count) {
+static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count, int prefer_planes = 0) {
     using C = T3<T, K>;
     T3Plan p;
     p.ntx = (int)((nx + C::VX - 1) / C::VX);
     p.nty = (int)((ny + C::VY - 1) / C::VY);
     const long long tiles = (long long)p.ntx * p.nty;
+    if (prefer_planes > 0) {  // the caller's tile preference wins over the makespan search
+        p.chunk_planes = (int)(prefer_planes < planes ? prefer_planes : planes);
+        p.nchunks = (planes + p.chunk_planes - 1) / p.chunk_planes;
+        p.blocks = tiles * p.nchunks;
+        return p;
+    }
     // one cache per instantiation, shared by every host thread (slab workers, planners)
     static std::map<std::array<long long, 6>, std::pair<int, long long>> cache;
     static std::mutex cache_mu;

@@ -262,7 +262,7 @@ struct W2dPlan {
 // that way and a launch costs the latency of ONE warp walking its chunk row by row, so they
 // are cut into short chunks (>= 4 rows) until every SM sub-partition has a few warps.
 // R > 1: the radius-R kernel of warp2dr.cuh, whose halo is K*R per side.
-static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count, int R = 1) {
+static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count, int R = 1, int prefer_rows = 0) {
     W2dPlan p;
     const int V = (W2D_WIDTH - ((K * R + 3) & ~3) - K * R) & ~3;
     p.nstrips = (int)((nx + V - 1) / V);
@@ -281,6 +281,7 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
         chunk_rows = (rows + nchunks - 1) / nchunks;
         if (chunk_rows < 4) chunk_rows = 4;
     }
+    if (prefer_rows > 0) chunk_rows = prefer_rows;  // the caller's tile preference wins
     if (chunk_rows > rows) chunk_rows = rows;
     if (chunk_rows < 1) chunk_rows = 1;
     p.chunk_rows = (int)chunk_rows;
@@ -291,9 +292,9 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
 
 template <class T, int SHAPE, int K>
 static cudaError_t launch_warp2d_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
-                                   long long oe, int sm_count, cudaStream_t st) {
+                                   long long oe, const Tuning& tn, cudaStream_t st) {
     if (oe <= ob) return cudaSuccess;
-    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, sm_count);
+    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, 1, tn.prefer_chunk);
     const T avg = Avg<T>::value(SHAPE, 2, 1);
     const unsigned blocks = (unsigned)((p.nitems + W2D_WARPS - 1) / W2D_WARPS);
     sweep_warp2d_kernel<T, SHAPE, K><<<blocks, 32 * W2D_WARPS, 0, st>>>(
@@ -303,9 +304,9 @@ static cudaError_t launch_warp2d_k(const T* in, T* out, const Grid& g, Domain do
 
 template <class T, int SHAPE>
 static cudaError_t launch_warp2d_s(const T* in, T* out, const Grid& g, Domain dom, int K,
-                                   long long ob, long long oe, int sm_count, cudaStream_t st) {
+                                   long long ob, long long oe, const Tuning& tn, cudaStream_t st) {
     switch (K) {
-#define SB200_W2D(KK) case KK: return launch_warp2d_k<T, SHAPE, KK>(in, out, g, dom, ob, oe, sm_count, st)
+#define SB200_W2D(KK) case KK: return launch_warp2d_k<T, SHAPE, KK>(in, out, g, dom, ob, oe, tn, st)
         SB200_W2D(1); SB200_W2D(2); SB200_W2D(3); SB200_W2D(4);
         SB200_W2D(5); SB200_W2D(6); SB200_W2D(7); SB200_W2D(8);
 #undef SB200_W2D
@@ -315,9 +316,9 @@ static cudaError_t launch_warp2d_s(const T* in, T* out, const Grid& g, Domain do
 
 template <class T>
 static cudaError_t launch_warp2d(const T* in, T* out, const Grid& g, int shape, Domain dom, int K,
-                                 long long ob, long long oe, int sm_count, cudaStream_t st) {
-    return shape == STAR ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, sm_count, st)
-                         : launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, sm_count, st);
+                                 long long ob, long long oe, const Tuning& tn, cudaStream_t st) {
+    return shape == STAR ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, tn, st)
+                         : launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, tn, st);
 }
 
 }  // namespace sb200

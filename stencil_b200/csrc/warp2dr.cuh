@@ -195,9 +195,9 @@ sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Doma
 
 template <class T, int R, int K>
 static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
-                                    long long oe, int sm_count, cudaStream_t st) {
+                                    long long oe, const Tuning& tn, cudaStream_t st) {
     if (oe <= ob) return cudaSuccess;
-    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, sm_count, R);
+    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, R, tn.prefer_chunk);
     const T avg = Avg<T>::value(STAR, 2, R);
     const unsigned blocks = (unsigned)((p.nitems + W2D_WARPS - 1) / W2D_WARPS);
     sweep_warp2dr_kernel<T, R, K><<<blocks, 32 * W2D_WARPS, 0, st>>>(
@@ -208,11 +208,11 @@ static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain d
 // 2-D star, radius 2..4, K fused steps (1 .. w2r_max_k(R, sizeof(T))).
 template <class T>
 static cudaError_t launch_warp2dr(const T* in, T* out, const Grid& g, Domain dom, int K, long long ob,
-                                  long long oe, int sm_count, cudaStream_t st) {
+                                  long long oe, const Tuning& tn, cudaStream_t st) {
     if (K < 1 || g.r < 2 || g.r > 4 || K > w2r_max_k(g.r, (int)sizeof(T))) return cudaErrorInvalidValue;
 #define SB200_W2R(RR, KK) \
     if constexpr (KK <= w2r_max_k(RR, (int)sizeof(T))) \
-        if (g.r == RR && K == KK) return launch_warp2dr_k<T, RR, KK>(in, out, g, dom, ob, oe, sm_count, st)
+        if (g.r == RR && K == KK) return launch_warp2dr_k<T, RR, KK>(in, out, g, dom, ob, oe, tn, st)
     SB200_W2R(2, 1); SB200_W2R(2, 2); SB200_W2R(2, 3); SB200_W2R(2, 4);
     SB200_W2R(3, 1); SB200_W2R(3, 2);
     SB200_W2R(4, 1); SB200_W2R(4, 2);

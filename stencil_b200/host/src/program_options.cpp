@@ -20,7 +20,9 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
 
     app.option("-s,--matrix-size", result.matrix_size, "The side length of the input matrix.").require();
     app.option("-i,--iteration", result.iterations, "The number of iterations.").require();
-    app.option("-b,--block-size", result.block_size, "The side length of the block into which the matrix is divided.")
+    app.option("-b,--block-size", result.block_size,
+               "The side length of the block into which the matrix is divided (CUDA: a hint; with "
+               "--block-as-tile the rows / planes each warp / CTA streams).")
         .require();
     app.option("-r,--radius", result.radius, "The radius of the stencil shape.", 1u);
     app.option("-R,--repeat", result.repeat_count, "The number of replicate runs for each method.", 1u);
@@ -36,6 +38,8 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
     app.option("--seed", result.seed, "Seed of the random initial condition.", 1ull);
     app.option("--kernel", result.kernel, "CUDA kernel family: auto, generic, warp2d, tma3d, resident2d, line1d.", std::string("auto"));
     app.option("--gpus", result.gpus, "GPUs of this box one CUDA run is spread over (z-slabs; y-slabs in 2-D).", 1u);
+    app.flag("--block-as-tile", result.block_as_tile,
+             "CUDA: use -b as the tile preference of the warp2d / tma3d kernels instead of the planner's choice.");
     app.option("--json", result.json_path, "Append one JSON record per method to this file.");
     app.option("--bmp", result.bmp_path, "Write the final 2-D field as a BMP heat map.");
 

@@ -116,3 +116,25 @@ def test_plan_host_logic(monkeypatch):
     assert capi.plan(capi.make_desc((96, 80, 72), 1, capi.STAR, capi.F64, 7), 7).pipeline_chunks == 3
     with pytest.raises(capi.StencilError):
         capi.plan(capi.make_desc((2000, 2000), 1, capi.STAR, capi.F32, 10, kernel=capi.KERNEL_RESIDENT2D), 10)
+
+
+def test_block_hint_is_a_tile_preference_when_asked(built):
+    """-b/--block-size (reference program_options.cpp:16-18) steers the chunk the planners give
+    one warp / CTA when SB200_FLAG_BLOCK_TILE is set, and is inert otherwise."""
+    base = capi.plan(capi.make_desc((4096, 4096), dtype=capi.F64, iterations=100, block_hint=64), 100)
+    assert base.kernel == capi.KERNEL_WARP2D
+    for b in (8, 64, 500):
+        p = capi.plan(capi.make_desc((4096, 4096), dtype=capi.F64, iterations=100, block_hint=b,
+                                     flags=capi.FLAG_BLOCK_TILE), 100)
+        assert p.chunk_extent == b and p.chunks == -(-4096 // b) and p.tiles_x == base.tiles_x
+    inert = capi.plan(capi.make_desc((4096, 4096), dtype=capi.F64, iterations=100, block_hint=8), 100)
+    assert (inert.chunk_extent, inert.chunks) == (base.chunk_extent, base.chunks)
+    p3 = capi.plan(capi.make_desc((512, 512, 512), dtype=capi.F64, iterations=100, block_hint=32,
+                                  flags=capi.FLAG_BLOCK_TILE), 100)
+    assert p3.kernel == capi.KERNEL_TMA3D and p3.chunk_extent == 32 and p3.chunks == 16
+    big = capi.plan(capi.make_desc((512, 512, 512), dtype=capi.F64, iterations=100, block_hint=100000,
+                                   flags=capi.FLAG_BLOCK_TILE), 100)
+    assert big.chunk_extent == 512 and big.chunks == 1
+    d = capi.make_desc((64, 64), flags=8)
+    lay = capi.Layout()
+    assert capi.lib().sb200_layout_for(ctypes.byref(d), 0, ctypes.byref(lay)) == capi.ERR_INVALID

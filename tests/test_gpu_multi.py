@@ -149,3 +149,23 @@ def test_cli_gpus_flag_self_check(gpu):
     r = subprocess.run([BIN, "-s", "64", "-i", "2", "-b", "1", "--gpus", str(have + 1), "-m", "CUDA"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 3, "asking for more GPUs than the box has is an error, not a silent single-GPU run"
+
+
+@pytest.mark.parametrize("n,shape,dtype,T,hint", [
+    ((300, 257), capi.BOX, np.float32, 9, 1), ((300, 257), capi.STAR, np.float64, 9, 7), ((300, 257), capi.BOX, np.float32, 9, 1000),
+    ((200, 150), capi.STAR, np.float32, 9, 5),
+    ((96, 80, 72), capi.STAR, np.float64, 5, 1), ((96, 80, 72), capi.STAR, np.float64, 5, 9), ((70, 66, 64), capi.BOX, np.float32, 4, 100),
+])
+def test_block_hint_tile_preference_keeps_the_bits(gpu, n, shape, dtype, T, hint):
+    """-b as the CUDA tile preference (SB200_FLAG_BLOCK_TILE): any chunk size, same result."""
+    code = oracle.F64 if dtype == np.float64 else oracle.F32
+    a = oracle.fill(n, 1, code, oracle.INIT_RANDOM, 2)
+    b = oracle.fill(n, 1, code, oracle.INIT_REF)
+    ga, gb = a.copy(), b.copy()
+    want = b if oracle.sweep(n, 1, shape, T, a, b, threads=oracle.max_threads()) else a
+    d = capi.make_desc(n, 1, shape, capi.F64 if dtype == np.float64 else capi.F32, T, block_hint=hint,
+                       flags=capi.FLAG_BLOCK_TILE)
+    t = capi.Timing()
+    capi.check(gpu.sb200_run_host(ctypes.byref(d), ga.ctypes.data, gb.ctypes.data, ctypes.byref(t)))
+    got = gb if T & 1 else ga
+    assert np.array_equal(want.view(np.uint8), got.view(np.uint8))
