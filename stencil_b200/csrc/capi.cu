@@ -79,6 +79,7 @@ struct MapKey {
     const void* ptr;
     int dtype;
     long long px, py, pl;
+    int box_x, box_y;  // TMA box; box_y < 0 marks a store map (interior extents, origin at interior (0,0))
 };
 struct MapEntry {
     MapKey key;
@@ -269,29 +270,37 @@ int set_smem_attr_once(F* kernel, size_t bytes) {
     return SB200_OK;
 }
 
-int get_tensor_map(const void* ptr, int dtype, const Grid& g, const CUtensorMap** out) {
-    for (auto& m : DS().maps)
-        if (m.key.ptr == ptr && m.key.dtype == dtype && m.key.px == g.pitch_x &&
-            m.key.py == g.pitch_y && m.key.pl == g.planes) {
+// Tensor maps of one device grid.  Load maps (store == false) span the whole allocation, halo
+// included, with box_x x box_y boxes (out-of-range parts are zero-filled).  Store maps span the
+// INTERIOR in x and y — origin at interior (0, 0), every plane of the allocation in z — so that
+// the TMA unit clips what a ragged tile holds beyond the grid and the Dirichlet halo is never
+// written.
+int get_tensor_map(const void* ptr, int dtype, const Grid& g, int box_x, int box_y, bool store,
+                   const CUtensorMap** out) {
+    State& D = DS();
+    const int key_by = store ? -box_y : box_y;
+    for (auto& m : D.maps)
+        if (m.key.ptr == ptr && m.key.dtype == dtype && m.key.px == g.pitch_x && m.key.py == g.pitch_y &&
+            m.key.pl == g.planes && m.key.box_x == box_x && m.key.box_y == key_by) {
             *out = &m.map;
             return SB200_OK;
         }
     MapEntry me;
-    me.key = {ptr, dtype, g.pitch_x, g.pitch_y, g.planes};
+    me.key = {ptr, dtype, g.pitch_x, g.pitch_y, g.planes, box_x, key_by};
     const size_t es = esize(dtype);
-    cuuint64_t dims[3] = {(cuuint64_t)g.pitch_x, (cuuint64_t)g.pitch_y, (cuuint64_t)g.planes};
+    cuuint64_t dims[3] = {(cuuint64_t)(store ? g.n[0] : g.pitch_x), (cuuint64_t)(store ? g.n[1] : g.pitch_y),
+                          (cuuint64_t)g.planes};
     cuuint64_t strides[2] = {(cuuint64_t)g.pitch_x * es, (cuuint64_t)g.pitch_x * g.pitch_y * es};
-    cuuint32_t box[3] = {(cuuint32_t)(dtype == SB200_F64 ? T3<double, 1>::BX : T3<float, 1>::BX),
-                         (cuuint32_t)T3<double, 1>::BY, 1};
+    cuuint32_t box[3] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1};
     cuuint32_t estr[3] = {1, 1, 1};
+    char* base = (char*)const_cast<void*>(ptr) + (store ? ((size_t)g.oy * g.pitch_x + g.ox) * es : 0);
     CUresult r = g_encode(&me.map, dtype == SB200_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
-                          3, const_cast<void*>(ptr), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                          3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SB200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    if (DS().maps.size() >= 64) DS().maps.erase(DS().maps.begin());
-    DS().maps.push_back(me);
-    *out = &DS().maps.back().map;
+    if (D.maps.size() >= 64) D.maps.erase(D.maps.begin());
+    D.maps.push_back(me);
+    *out = &D.maps.back().map;
     return SB200_OK;
 }
 
@@ -304,8 +313,12 @@ int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, lo
     if (int rc = linked ? set_smem_attr_once(sweep_tma3d_kernel<T, K, SHAPE, true>, C::SMEM)
                         : set_smem_attr_once(sweep_tma3d_kernel<T, K, SHAPE, false>, C::SMEM))
         return rc;
-    const CUtensorMap* map = nullptr;
-    if (int rc = get_tensor_map(in, dtype, g, &map)) return rc;
+    // copies: a later insertion may evict / move cache entries
+    const CUtensorMap* mp = nullptr;
+    if (int rc = get_tensor_map(in, dtype, g, C::BX, C::BY, false, &mp)) return rc;
+    const CUtensorMap imap = *mp;
+    if (int rc = get_tensor_map(out, dtype, g, C::VX, C::VY, true, &mp)) return rc;
+    const CUtensorMap omap = *mp;
     const T3Plan p = t3_plan<T, K>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
     const T avg = Avg<T>::value(SHAPE, 3, 1);
     if (linked) {
@@ -315,10 +328,10 @@ int launch_tma3d_k(const T* in, T* out, int dtype, const Grid& g, Domain dom, lo
         if (nc < 1) nc = 1;
         link.nchunks = (int)nc;
         sweep_tma3d_kernel<T, K, SHAPE, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
-            *map, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
+            imap, omap, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
     } else {
         sweep_tma3d_kernel<T, K, SHAPE, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
-            *map, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link_in);
+            imap, omap, in, out, g, dom, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link_in);
     }
     CU_TRY(cudaGetLastError());
     return SB200_OK;
@@ -340,7 +353,6 @@ int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domai
     switch (K) {
         case 1: return launch_tma3d_k<T, 1, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
         case 2: return launch_tma3d_k<T, 2, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
-        case 3: return launch_tma3d_k<T, 3, STAR>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
         default: return fail(SB200_ERR_INVALID, "TMA3D time block %d out of range", K);
     }
 }
@@ -598,11 +610,11 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
         if (desc->dtype == SB200_F64)
             p = k == 1 ? t3_plan<double, 1>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
                 : k == 2 ? t3_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
-                         : t3_plan<double, 3>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
+                         : t3_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
         else
             p = k == 1 ? t3_plan<float, 1>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
                 : k == 2 ? t3_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
-                         : t3_plan<float, 3>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
+                         : t3_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
         info->tiles_x = (uint32_t)p.ntx;
         info->tiles_y = (uint32_t)p.nty;
         info->chunks = (uint32_t)p.nchunks;
@@ -770,13 +782,13 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
         switch (steps) {
             case 1: { auto p = t3_plan<double, 1>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
             case 2: { auto p = t3_plan<double, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
-            default: { auto p = t3_plan<double, 3>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<double, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
         }
     } else {
         switch (steps) {
             case 1: { auto p = t3_plan<float, 1>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
             case 2: { auto p = t3_plan<float, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
-            default: { auto p = t3_plan<float, 3>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
+            default: { auto p = t3_plan<float, 2>(g.n[0], g.n[1], 1, DS().sm_count); ntx = p.ntx; nty = p.nty; } break;
         }
     }
     if (arrivals) *arrivals = (uint32_t)(ntx * nty);

@@ -33,7 +33,13 @@ namespace sb200 {
 template <class T, int K> struct T3 {
     static constexpr int PXV = 16 / (int)sizeof(T);  // x points per thread (128-bit)
     static constexpr int PY = 4;                     // rows per thread
+#ifdef SB200_T3_TYN  // experiment: 64 x 32 tiles, two CTAs per SM
+    static constexpr int TXN = 32, TYN = SB200_T3_TYN;
+    static constexpr int CTAS_PER_SM = 16 / SB200_T3_TYN;
+#else
     static constexpr int TXN = 32, TYN = 16;
+    static constexpr int CTAS_PER_SM = 1;
+#endif
     static constexpr int THREADS = TXN * TYN;
     static constexpr int BX = TXN * PXV, BY = TYN * PY;
     static constexpr int HLX = (K + PXV - 1) / PXV * PXV;
@@ -45,8 +51,12 @@ template <class T, int K> struct T3 {
     // levels 1..K-1 only publish each thread's first and last row (what its y-neighbour
     // threads need); the rows in between stay in the owner's registers
     static constexpr int EDGE = TYN * 2 * BX;  // elements per edge buffer
+    // the last level's planes leave through a dense VX x VY staging tile in shared memory and
+    // a TMA store (two slots: the store of step j reads its slot while step j+1 fills the other)
+    static constexpr int STAGE = VX * VY;  // elements
+    static constexpr size_t STAGE_BYTES = ((size_t)STAGE * sizeof(T) + 127) / 128 * 128;
     static constexpr size_t SMEM =
-        PLANE_BYTES * STAGES + (size_t)EDGE * sizeof(T) * 2 * (K - 1) + 8 * STAGES + 128;
+        PLANE_BYTES * STAGES + (size_t)EDGE * sizeof(T) * 2 * (K - 1) + 2 * STAGE_BYTES + 8 * STAGES + 128;
 };
 // tools/sm_bound_probe.sh builds a second library with -DSB200_PROBE_ZWRAP=8: every CTA then
 // streams the same 8 planes over and over (loads and stores stay in L2, results are garbage),
@@ -57,7 +67,7 @@ template <class T, int K> struct T3 {
 #else
 #define T3_PROBE_Z(j) (j)
 #endif
-constexpr int T3_MAXK = 3;      // star
+constexpr int T3_MAXK = 2;      // star (a third level does not fit the register file: profiles/r01f_ptxas.md)
 constexpr int T3_MAXK_BOX = 2;  // box (27-point)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -84,6 +94,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+// Store of a dense smem box into the tensor (bulk async-group of the calling thread); parts of
+// the box outside the tensor's extents are clipped by the TMA unit.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+                 "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() {  // every committed store has read its smem
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {  // ... and has been written
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar,
                                             int c0, int c1, int c2) {
     asm volatile(
@@ -95,8 +119,18 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
 
 template <class T, int N> struct VecN;
 template <> struct VecN<float, 4> {
+    static __device__ __forceinline__ void lds(uint32_t a, float* v) {
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(a));
+    }
+    static __device__ __forceinline__ void sts(uint32_t a, const float* v) {
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+    }
     static __device__ __forceinline__ void ld(const float* p, float* v) {
         const float4 f = *reinterpret_cast<const float4*>(p);
+        v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+    }
+    static __device__ __forceinline__ void ldcg(const float* p, float* v) {
+        const float4 f = __ldcg(reinterpret_cast<const float4*>(p));
         v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
     }
     static __device__ __forceinline__ void st(float* p, const float* v) {
@@ -104,8 +138,18 @@ template <> struct VecN<float, 4> {
     }
 };
 template <> struct VecN<double, 2> {
+    static __device__ __forceinline__ void lds(uint32_t a, double* v) {
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "r"(a));
+    }
+    static __device__ __forceinline__ void sts(uint32_t a, const double* v) {
+        asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(v[0]), "d"(v[1]) : "memory");
+    }
     static __device__ __forceinline__ void ld(const double* p, double* v) {
         const double2 f = *reinterpret_cast<const double2*>(p);
+        v[0] = f.x; v[1] = f.y;
+    }
+    static __device__ __forceinline__ void ldcg(const double* p, double* v) {
+        const double2 f = __ldcg(reinterpret_cast<const double2*>(p));
         v[0] = f.x; v[1] = f.y;
     }
     static __device__ __forceinline__ void st(double* p, const double* v) {
@@ -137,15 +181,23 @@ __device__ __forceinline__ void t3_level(const T (&up)[PXV], const T (&c)[PY][PX
                                          T (&o)[PY][PXV]) {
 #pragma unroll
     for (int i = 0; i < PY; ++i) {
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 8)  // ablation (wrong results): no shuffles
+        const T lft = c[i][PXV - 1], rgt = c[i][0];
+#else
         const T lft = __shfl_up_sync(0xffffffffu, c[i][PXV - 1], 1);
         const T rgt = __shfl_down_sync(0xffffffffu, c[i][0], 1);
+#endif
 #pragma unroll
         for (int k = 0; k < PXV; ++k) {
             const T xl = k == 0 ? lft : c[i][k - 1];
             const T xr = k == PXV - 1 ? rgt : c[i][k + 1];
             const T yl = i == 0 ? up[k] : c[i - 1][k];
             const T yr = i == PY - 1 ? dn[k] : c[i + 1][k];
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 2)
+            const T sum = add_rn(add_rn(add_rn(xl, xr), yl), yr);  // experiment: without the oracle's 0 + xl
+#else
             const T sum = add_rn(add_rn(add_rn(add_rn(T(0), xl), xr), yl), yr);
+#endif
             o[i][k] = mul_rn(add_rn(L.t[i][k], c[i][k]), avg);
             L.t[i][k] = add_rn(sum, cm1[i][k]);
         }
@@ -266,9 +318,9 @@ __device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsi
 }
 
 template <class T, int K, int SHAPE, bool LINKED>
-__global__ void __launch_bounds__(T3<T, K>::THREADS, 1)
-sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict__ in,
-                   T* __restrict__ out, Grid g, Domain dom, long long ob, long long oe, int ntx, int nty,
+__global__ void __launch_bounds__(T3<T, K>::THREADS, T3<T, K>::CTAS_PER_SM)
+sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap omap,
+                   const T* __restrict__ in, T* __restrict__ out, Grid g, Domain dom, long long ob, long long oe, int ntx, int nty,
                    int chunk_planes, T avg, const SlabLinkDev link) {
     using C = T3<T, K>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
@@ -278,7 +330,8 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
     unsigned char* base = smem_raw + ((128 - (smem_u32(smem_raw) & 127)) & 127);
     T* ring = reinterpret_cast<T*>(base);
     T* ebuf = ring + (size_t)S * C::PLANE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(ebuf + (size_t)2 * (K - 1) * C::EDGE);
+    unsigned char* stage = reinterpret_cast<unsigned char*>(ebuf + (size_t)2 * (K - 1) * C::EDGE);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stage + 2 * C::STAGE_BYTES);
 
     const int tid = threadIdx.x;
     const int tx = tid & 31, ty = tid >> 5;
@@ -341,7 +394,16 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
     const bool col_ok = lx >= C::HLX && lx < C::HLX + C::VX && gx < g.n[0];
     const bool col_full = gx + PXV <= g.n[0];
     if (!col_ok) rows_ok = 0;
-    const bool store_fast = col_full && rows_ok == (1u << PY) - 1u;
+    // staging tile of the TMA store: rows / columns of the tile's valid VX x VY region, whether
+    // or not they lie inside the grid (the TMA unit clips)
+    unsigned s_rows = 0;
+#pragma unroll
+    for (int i = 0; i < PY; ++i)
+        if (ly + i >= K && ly + i < K + C::VY) s_rows |= 1u << i;
+    if (!(lx >= C::HLX && lx < C::HLX + C::VX)) s_rows = 0;
+    const int s_off = (ly - K) * C::VX + (lx - C::HLX);
+    // store coordinates in the output map (x, y: interior origin; z: plane index of the allocation)
+    const int ox0 = tix * C::VX, oy0 = tiy * C::VY, oz0 = (int)(z_first + g.oz);
     const int toff = ly * C::BX + lx;
     const int up_off = ly > 0 ? -C::BX : 0;
     const int dn_off = ly + PY < C::BY ? PY * C::BX : (PY - 1) * C::BX;
@@ -376,10 +438,18 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
                 for (int l = 0; l < K - 1; ++l) O[l][s][i][k] = T(0);
             }
 
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
+    // experiment: 32-bit shared-window addresses made opaque to the compiler, so it keeps them
+    // in registers instead of rematerialising them from SR_CgaCtaId inside the plane loop
+    uint32_t ring_s = smem_u32(ring);
+    asm volatile("" : "+r"(ring_s));
+    uint32_t ebuf_s = ring_s + (uint32_t)(S * C::PLANE_BYTES);
+    asm volatile("" : "+r"(ebuf_s));
+#endif
     const long long plane_stride = g.pitch_x * g.pitch_y;
     const long long row_stride = g.pitch_x;
+    (void)row_stride;
     // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
-    T* __restrict__ outp_run = out + g.idx(gx, gy, z_first - 2 * K + 1);
     // One time level of one plane step.  L = level index (level L+1 of the fused block),
     // P = j & 1.  Level L consumes the plane its lower level emitted on the PREVIOUS step
     // (registers + the edge rows published in shared memory), so one barrier per step
@@ -390,15 +460,29 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
         if constexpr (L == 0) {
             const int st = j & (S - 1);
             if (j < nin) mbar_wait(&bars[st], (uint32_t)(j / S) & 1u);
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
+            const uint32_t src = ring_s + (uint32_t)((st * C::PLANE + toff) * (int)sizeof(T));
+            VecN<T, PXV>::lds(src + (uint32_t)(up_off * (int)sizeof(T)), up);
+#pragma unroll
+            for (int i = 0; i < PY; ++i) VecN<T, PXV>::lds(src + (uint32_t)(i * C::BX * (int)sizeof(T)), R[P][i]);
+            VecN<T, PXV>::lds(src + (uint32_t)(dn_off * (int)sizeof(T)), dn);
+#else
             const T* src = ring + (size_t)st * C::PLANE + toff;
             VecN<T, PXV>::ld(src + up_off, up);
 #pragma unroll
             for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[P][i]);
             VecN<T, PXV>::ld(src + dn_off, dn);
+#endif
         } else {
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
+            const uint32_t eb = ebuf_s + (uint32_t)((2 * (L - 1) + (P ^ 1)) * C::EDGE * (int)sizeof(T));
+            VecN<T, PXV>::lds(eb + (uint32_t)(e_up * (int)sizeof(T)), up);
+            VecN<T, PXV>::lds(eb + (uint32_t)(e_dn * (int)sizeof(T)), dn);
+#else
             const T* eb = ebuf + (size_t)(2 * (L - 1) + (P ^ 1)) * C::EDGE;
             VecN<T, PXV>::ld(eb + e_up, up);
             VecN<T, PXV>::ld(eb + e_dn, dn);
+#endif
         }
         const T (&c)[PY][PXV] = *(L == 0 ? &R[P] : &O[L > 0 ? L - 1 : 0][P ^ 1]);
         const T (&cm1)[PY][PXV] = *(L == 0 ? &R[P ^ 1] : &O[L > 0 ? L - 1 : 0][P]);
@@ -415,9 +499,15 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
                     for (int k = 0; k < PXV; ++k)
                         if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
             }
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
+            const uint32_t wb = ebuf_s + (uint32_t)(((2 * L + P) * C::EDGE + e_own) * (int)sizeof(T));
+            VecN<T, PXV>::sts(wb, o[0]);
+            VecN<T, PXV>::sts(wb + (uint32_t)(C::BX * (int)sizeof(T)), o[PY - 1]);
+#else
             T* wb = ebuf + (size_t)(2 * L + P) * C::EDGE + e_own;
             VecN<T, PXV>::st(wb, o[0]);
             VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
+#endif
         } else {
             // The last level needs no pass-through fix-up: only updatable points of planes
             // inside the update domain are ever stored.  The box variant drops it (and with it
@@ -434,43 +524,54 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
                     for (int k = 0; k < PXV; ++k)
                         if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
             }
-            if (pe >= p_out_lo && pe < p_out_hi) {
-#ifdef SB200_PROBE_ZWRAP
-                T* __restrict__ outp = outp_run - (long long)((pe - K) & ~(SB200_PROBE_ZWRAP - 1)) * plane_stride;
-#else
-                T* __restrict__ outp = outp_run;
-#endif
-                if (store_fast) {
+            // out through the staging tile: dense VX x VY, this thread's rows at (ly - K, lx - HLX)
+            if (pe >= p_out_lo && pe < p_out_hi && s_rows) {
+                T* sp = reinterpret_cast<T*>(stage + (size_t)P * C::STAGE_BYTES) + s_off;
 #pragma unroll
-                    for (int i = 0; i < PY; ++i) VecN<T, PXV>::st(outp + i * row_stride, o[i]);
-                } else if (rows_ok) {
-#pragma unroll
-                    for (int i = 0; i < PY; ++i) {
-                        if (rows_ok & (1u << i)) {
-                            if (col_full) {
-                                VecN<T, PXV>::st(outp + i * row_stride, o[i]);
-                            } else {
-#pragma unroll
-                                for (int k = 0; k < PXV; ++k)
-                                    if (gx + k < g.n[0]) outp[i * row_stride + k] = o[i][k];
-                            }
-                        }
-                    }
-                }
+                for (int i = 0; i < PY; ++i)
+                    if (s_rows & (1u << i)) VecN<T, PXV>::st(sp + i * C::VX, o[i]);
             }
         }
     };
     auto step = [&](auto Pc, int j) {
         // higher levels first: they consume what the level below emitted one step earlier
+#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 1)
+        if (K == 2 && ((ty >> 2) & 1)) {  // experiment: half of the warps of a sub-partition run the levels in the other order
+            level(IC<0>{}, Pc, j);
+            if constexpr (K > 1) level(IC<1>{}, Pc, j);
+        } else
+#endif
+        {
         if constexpr (K > 2) level(IC<2>{}, Pc, j);
         if constexpr (K > 1) level(IC<1>{}, Pc, j);
         level(IC<0>{}, Pc, j);
-        outp_run += plane_stride;
+        }
+        // The plane the last level just staged (local index j - 2K + 1) leaves through a TMA
+        // store issued by thread 0 after the barrier: 512-byte rows straight into L2 without
+        // passing the LSU (an STG version of this kernel spent a third of its time on its
+        // stores: profiles/r02d_kernel_experiments.log), clipped to the interior by the TMA
+        // unit, so ragged tiles need no predication.  Slot P is refilled two steps later; the
+        // store that read the OTHER slot is waited for before the barrier that lets step j+1
+        // overwrite it.
+        constexpr int P = decltype(Pc)::value;
+        const int po = j - 2 * K + 1;
+        const bool storing = po >= p_out_lo && po < p_out_hi;
+        if (storing) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (tid == 0) tma_store_wait_read();
         __syncthreads();
-        if (tid == 0 && j + S < nin) {
-            const int st = j & (S - 1);
-            mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
-            tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + T3_PROBE_Z(j + S));
+        if (tid == 0) {
+            if (storing)
+                tma_store_3d(&omap, stage + (size_t)P * C::STAGE_BYTES, ox0, oy0,
+#ifdef SB200_PROBE_ZWRAP
+                             oz0 + K + ((po - K) & (SB200_PROBE_ZWRAP - 1)));
+#else
+                             oz0 + po);
+#endif
+            if (j + S < nin) {
+                const int st = j & (S - 1);
+                mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
+                tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + T3_PROBE_Z(j + S));
+            }
         }
     };
     // steps past nsteps (loop rounded up to the phase count) wait for nothing and store nothing
@@ -479,12 +580,16 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
         step(IC<0>{}, j);
         step(IC<1>{}, j + 1);
     }
+    if (tid == 0) tma_store_wait_all();  // the staging slots outlive the CTA otherwise
     if (LINKED && (is_lo || is_hi)) {
         // Face push, after the z stream so the plane loop carries no link code at all: every
-        // thread copies the face-plane points IT stored (its own writes, so no barrier is
-        // needed before the read-back) into the neighbour's ghost planes with 128-bit
-        // stores over NVLink; after the barrier thread 0 publishes them system-wide and
-        // counts this CTA in on the neighbour's arrival counter.
+        // thread copies the face-plane points of its part of the tile (written by this CTA's TMA
+        // stores, all complete: thread 0 waited, then the barrier and the proxy fence) into the
+        // neighbour's ghost planes with 128-bit stores over NVLink; after the next barrier
+        // thread 0 publishes them system-wide and counts this CTA in on the neighbour's
+        // arrival counter.
+        __syncthreads();
+        asm volatile("fence.proxy.async.global;" ::: "memory");
         T* home = out + g.idx(gx, gy, 0);
 #pragma unroll 1
         for (int side = 0; side < 2; ++side) {
@@ -500,12 +605,12 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const T* __restrict
                     if (rows_ok & (1u << i)) {
                         if (col_full) {
                             T v[PXV];
-                            VecN<T, PXV>::ld(src + i * row_stride, v);
+                            VecN<T, PXV>::ldcg(src + i * row_stride, v);
                             VecN<T, PXV>::st(src + rdelta + i * row_stride, v);
                         } else {
 #pragma unroll
                             for (int k = 0; k < PXV; ++k)
-                                if (gx + k < g.n[0]) src[rdelta + i * row_stride + k] = src[i * row_stride + k];
+                                if (gx + k < g.n[0]) src[rdelta + i * row_stride + k] = __ldcg(src + i * row_stride + k);
                         }
                     }
                 }
@@ -562,7 +667,7 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
             const double dfull = cp + 3 * K - 1 + startup;
             const double dlast = (planes - (nc - 1) * cp) + 3 * K - 1 + startup;
             // min-heap of SM free times
-            heap.assign((size_t)sm_count, 0.0);
+            heap.assign((size_t)sm_count * C::CTAS_PER_SM, 0.0);
             auto push_cta = [&](double d) {
                 std::pop_heap(heap.begin(), heap.end(), std::greater<double>());
                 heap.back() += d;
