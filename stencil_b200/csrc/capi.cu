@@ -288,8 +288,12 @@ int get_tensor_map(const void* ptr, int dtype, const Grid& g, int box_x, int box
     MapEntry me;
     me.key = {ptr, dtype, g.pitch_x, g.pitch_y, g.planes, box_x, key_by};
     const size_t es = esize(dtype);
-    cuuint64_t dims[3] = {(cuuint64_t)(store ? g.n[0] : g.pitch_x), (cuuint64_t)(store ? g.n[1] : g.pitch_y),
-                          (cuuint64_t)g.planes};
+    // store maps end at the last full 16 bytes of an interior row (the unit the TMA clips in);
+    // the kernel stores the ragged end itself
+    const long long per16 = 16 / (long long)esize(dtype);
+    cuuint64_t dims[3] = {(cuuint64_t)(store ? g.n[0] / per16 * per16 : g.pitch_x),
+                          (cuuint64_t)(store ? g.n[1] : g.pitch_y), (cuuint64_t)g.planes};
+    if (store && dims[0] == 0) dims[0] = (cuuint64_t)per16;  // a valid descriptor; nothing of it is ever in range
     cuuint64_t strides[2] = {(cuuint64_t)g.pitch_x * es, (cuuint64_t)g.pitch_x * g.pitch_y * es};
     cuuint32_t box[3] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1};
     cuuint32_t estr[3] = {1, 1, 1};
@@ -343,6 +347,13 @@ template <class T>
 int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domain dom, int K,
                  long long ob, long long oe, cudaStream_t st, const SlabLinkDev& link = kNoLink,
                  int prefer_chunk = 0) {
+    if (shape == BOXSEP) {  // SB200_FLAG_REASSOCIATE
+        switch (K) {
+            case 1: return launch_tma3d_k<T, 1, BOXSEP>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
+            case 2: return launch_tma3d_k<T, 2, BOXSEP>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
+            default: return fail(SB200_ERR_INVALID, "TMA3D box time block %d out of range", K);
+        }
+    }
     if (shape == SB200_BOX) {
         switch (K) {
             case 1: return launch_tma3d_k<T, 1, BOX>(in, out, dtype, g, dom, ob, oe, st, link, prefer_chunk);
@@ -404,6 +415,11 @@ int check_choice(const sb200_desc* d, const Choice& c) {
     return SB200_OK;
 }
 
+// Kernel shape of the tma3d family: the separable box under SB200_FLAG_REASSOCIATE.
+int t3_shape(const sb200_desc* d) {
+    return d->shape == SB200_BOX && (d->flags & SB200_FLAG_REASSOCIATE) ? (int)BOXSEP : d->shape;
+}
+
 // -b/--block-size as a tile preference (opt-in): rows / planes one CTA or warp streams.
 int tile_pref(const sb200_desc* d) {
     return (d->flags & SB200_FLAG_BLOCK_TILE) && d->block_hint > 0 ? (int)(d->block_hint > (1u << 20) ? (1u << 20) : d->block_hint) : 0;
@@ -425,7 +441,8 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
                 CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
-            return launch_tma3d<T>(a, b, d->dtype, g, d->shape, dom, k, ob, oe, st, kNoLink, tile_pref(d));
+            return launch_tma3d<T>(a, b, d->dtype, g, t3_shape(d),
+                                   dom, k, ob, oe, st, kNoLink, tile_pref(d));
         case SB200_KERNEL_LINE1D:
             CU_TRY(launch_line1d<T>(a, b, g, d->shape, k, st));
             return SB200_OK;
@@ -794,8 +811,8 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     if (arrivals) *arrivals = (uint32_t)(ntx * nty);
     cudaStream_t st = (cudaStream_t)stream;
     if (desc->dtype == SB200_F64)
-        return launch_tma3d<double>((const double*)a, (double*)b, desc->dtype, g, desc->shape, dom, (int)steps, ob, oe, st, L);
-    return launch_tma3d<float>((const float*)a, (float*)b, desc->dtype, g, desc->shape, dom, (int)steps, ob, oe, st, L);
+        return launch_tma3d<double>((const double*)a, (double*)b, desc->dtype, g, t3_shape(desc), dom, (int)steps, ob, oe, st, L);
+    return launch_tma3d<float>((const float*)a, (float*)b, desc->dtype, g, t3_shape(desc), dom, (int)steps, ob, oe, st, L);
 }
 
 int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int init, uint64_t seed,

@@ -10,7 +10,10 @@
 
 namespace sb200 {
 
-enum : int { STAR = 0, BOX = 1 };
+// BOXSEP: the box stencil with separable partial sums (x, then y, then z: 8 operations per
+// point instead of 28), an internal kernel variant chosen under SB200_FLAG_REASSOCIATE; agrees
+// with the reference order within the north-star tolerance, not bit for bit.
+enum : int { STAR = 0, BOX = 1, BOXSEP = 2 };
 enum : int { F32 = 0, F64 = 1 };
 
 // Geometry of one device grid (one slab).  Coordinates passed to idx() are interior

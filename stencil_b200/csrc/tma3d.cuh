@@ -37,7 +37,9 @@ template <class T, int K> struct T3 {
     static constexpr int TXN = 32, TYN = SB200_T3_TYN;
     static constexpr int CTAS_PER_SM = 16 / SB200_T3_TYN;
 #else
-    static constexpr int TXN = 32, TYN = 16;
+    // K = 3 keeps nine plane-sized arrays of state per thread: 12 warps (64 x 48 tiles) leave
+    // every thread 168 registers instead of 128
+    static constexpr int TXN = 32, TYN = K >= 3 ? 12 : 16;
     static constexpr int CTAS_PER_SM = 1;
 #endif
     static constexpr int THREADS = TXN * TYN;
@@ -67,7 +69,8 @@ template <class T, int K> struct T3 {
 #else
 #define T3_PROBE_Z(j) (j)
 #endif
-constexpr int T3_MAXK = 2;      // star (a third level does not fit the register file: profiles/r01f_ptxas.md)
+constexpr int T3_MAXK = 2;      // star: K = 3 (12-warp tiles, 168 registers) is correct but slower, 599 vs 705
+                                // GStencil/s on config 2 (profiles/r02e_tma_store_probe.log); not instantiated
 constexpr int T3_MAXK_BOX = 2;  // box (27-point)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -119,12 +122,6 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
 
 template <class T, int N> struct VecN;
 template <> struct VecN<float, 4> {
-    static __device__ __forceinline__ void lds(uint32_t a, float* v) {
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(a));
-    }
-    static __device__ __forceinline__ void sts(uint32_t a, const float* v) {
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
-    }
     static __device__ __forceinline__ void ld(const float* p, float* v) {
         const float4 f = *reinterpret_cast<const float4*>(p);
         v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
@@ -138,12 +135,6 @@ template <> struct VecN<float, 4> {
     }
 };
 template <> struct VecN<double, 2> {
-    static __device__ __forceinline__ void lds(uint32_t a, double* v) {
-        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "r"(a));
-    }
-    static __device__ __forceinline__ void sts(uint32_t a, const double* v) {
-        asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(v[0]), "d"(v[1]) : "memory");
-    }
     static __device__ __forceinline__ void ld(const double* p, double* v) {
         const double2 f = *reinterpret_cast<const double2*>(p);
         v[0] = f.x; v[1] = f.y;
@@ -257,7 +248,45 @@ __device__ __forceinline__ void t3_level(const T (&up)[PXV], const T (&c)[PY][PX
     }
 }
 
+// ---- 27-point box, separable sums (SB200_FLAG_REASSOCIATE) -----------------------------------
+// row sums rs = (xl + xc) + xr of the PY + 2 rows a thread sees, plane sums sxy = (rs(y-1) +
+// rs(y)) + rs(y+1), then the z chain with the same two accumulators as the exact variant:
+// out(a-1) = ((sxy(a-2) + sxy(a-1)) + sxy(a)) * avg.  8 operations per point instead of 28, in
+// an order the reference does not use: equal within 1e-12 (fp64) / 1e-5 (fp32) relative.
+template <class T, int PXV, int PY> struct T3BoxSep : T3Box<T, PXV, PY> {};
+
+template <class T, int PXV, int PY>
+__device__ __forceinline__ void t3_level(const T (&up)[PXV], const T (&c)[PY][PXV], const T (&dn)[PXV],
+                                         const T (&)[PY][PXV], T3BoxSep<T, PXV, PY>& L, T avg,
+                                         T (&o)[PY][PXV]) {
+    T rs_prev[PXV], rs_cur[PXV], rs_next[PXV];
+    auto row_sum = [&](const T (&row)[PXV], T (&rs)[PXV]) {
+        const T lft = __shfl_up_sync(0xffffffffu, row[PXV - 1], 1);
+        const T rgt = __shfl_down_sync(0xffffffffu, row[0], 1);
+#pragma unroll
+        for (int k = 0; k < PXV; ++k)
+            rs[k] = add_rn(add_rn(k == 0 ? lft : row[k - 1], row[k]), k == PXV - 1 ? rgt : row[k + 1]);
+    };
+    row_sum(up, rs_prev);
+    row_sum(c[0], rs_cur);
+#pragma unroll
+    for (int i = 0; i < PY; ++i) {
+        if (i + 1 < PY) row_sum(c[i + 1 < PY ? i + 1 : i], rs_next);
+        else row_sum(dn, rs_next);
+#pragma unroll
+        for (int k = 0; k < PXV; ++k) {
+            const T sxy = add_rn(add_rn(rs_prev[k], rs_cur[k]), rs_next[k]);
+            o[i][k] = mul_rn(add_rn(L.b[i][k], sxy), avg);
+            L.b[i][k] = add_rn(L.a[i][k], sxy);
+            L.a[i][k] = sxy;
+            rs_prev[k] = rs_cur[k];
+            rs_cur[k] = rs_next[k];
+        }
+    }
+}
+
 template <class T, int PXV, int PY, int SHAPE> struct T3LevelSel { using type = T3Star<T, PXV, PY>; };
+template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOXSEP> { using type = T3BoxSep<T, PXV, PY>; };
 template <class T, int PXV, int PY> struct T3LevelSel<T, PXV, PY, BOX> { using type = T3Box<T, PXV, PY>; };
 
 template <int V> struct IC { static constexpr int value = V; };
@@ -372,7 +401,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     const int cx = (int)(gx0 + g.ox), cy = (int)(gy0 + g.oy);
     const int cz0 = (int)(z_first + g.oz);
     if (tid == 0) {
-        for (int s = 0; s < S && s < nin; ++s) {
+        for (int s = 0; s < S - 1 && s < nin; ++s) {
             mbar_expect_tx(&bars[s], (uint32_t)C::PLANE_BYTES);
             tma_load_3d(ring + (size_t)s * C::PLANE, &tmap, &bars[s], cx, cy, cz0 + T3_PROBE_Z(s));
         }
@@ -402,6 +431,7 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         if (ly + i >= K && ly + i < K + C::VY) s_rows |= 1u << i;
     if (!(lx >= C::HLX && lx < C::HLX + C::VX)) s_rows = 0;
     const int s_off = (ly - K) * C::VX + (lx - C::HLX);
+    const int x_tail = gx == g.n[0] / PXV * PXV ? (int)(g.n[0] - gx) : 0;  // 0 .. PXV-1
     // store coordinates in the output map (x, y: interior origin; z: plane index of the allocation)
     const int ox0 = tix * C::VX, oy0 = tiy * C::VY, oz0 = (int)(z_first + g.oz);
     const int toff = ly * C::BX + lx;
@@ -422,13 +452,22 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     // every step: before its first real plane a level only sees the zero-initialised rings
     // (its state stays zero), and what the levels compute after the last streamed plane lies
     // beyond the last stored plane.
-    T R[2][PY][PXV];
-    T O[K > 1 ? K - 1 : 1][2][PY][PXV];
+    // The star needs the previous plane of every level for its arithmetic (the z-low term is
+    // added after the in-plane ones), so R and O are two-slot rings indexed by the phase.  The
+    // box variants only ever read the previous plane in the pass-through fix-up of a level that
+    // is not the last: they keep ONE slot (6 plane-sized arrays at K = 2 instead of 8: no
+    // spills) and the fix-up of level 0 re-reads the plane from the TMA ring, which therefore
+    // runs S-1 planes ahead, not S.
+    constexpr bool HIST = SHAPE == STAR;
+    static_assert(HIST || K <= 2, "box variants: the only level that is not the last one is level 0");
+    constexpr int NS = HIST ? 2 : 1;
+    T R[NS][PY][PXV];
+    T O[K > 1 ? K - 1 : 1][NS][PY][PXV];
     typename T3LevelSel<T, PXV, PY, SHAPE>::type lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
 #pragma unroll
-    for (int s = 0; s < 2; ++s)
+    for (int s = 0; s < NS; ++s)
 #pragma unroll
         for (int i = 0; i < PY; ++i)
 #pragma unroll
@@ -438,18 +477,8 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
                 for (int l = 0; l < K - 1; ++l) O[l][s][i][k] = T(0);
             }
 
-#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
-    // experiment: 32-bit shared-window addresses made opaque to the compiler, so it keeps them
-    // in registers instead of rematerialising them from SR_CgaCtaId inside the plane loop
-    uint32_t ring_s = smem_u32(ring);
-    asm volatile("" : "+r"(ring_s));
-    uint32_t ebuf_s = ring_s + (uint32_t)(S * C::PLANE_BYTES);
-    asm volatile("" : "+r"(ebuf_s));
-#endif
     const long long plane_stride = g.pitch_x * g.pitch_y;
     const long long row_stride = g.pitch_x;
-    (void)row_stride;
-    // the last level emits local plane (j - 2K + 1) at step j; keep a running pointer
     // One time level of one plane step.  L = level index (level L+1 of the fused block),
     // P = j & 1.  Level L consumes the plane its lower level emitted on the PREVIOUS step
     // (registers + the edge rows published in shared memory), so one barrier per step
@@ -460,54 +489,36 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         if constexpr (L == 0) {
             const int st = j & (S - 1);
             if (j < nin) mbar_wait(&bars[st], (uint32_t)(j / S) & 1u);
-#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
-            const uint32_t src = ring_s + (uint32_t)((st * C::PLANE + toff) * (int)sizeof(T));
-            VecN<T, PXV>::lds(src + (uint32_t)(up_off * (int)sizeof(T)), up);
-#pragma unroll
-            for (int i = 0; i < PY; ++i) VecN<T, PXV>::lds(src + (uint32_t)(i * C::BX * (int)sizeof(T)), R[P][i]);
-            VecN<T, PXV>::lds(src + (uint32_t)(dn_off * (int)sizeof(T)), dn);
-#else
             const T* src = ring + (size_t)st * C::PLANE + toff;
             VecN<T, PXV>::ld(src + up_off, up);
 #pragma unroll
-            for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[P][i]);
+            for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[HIST ? P : 0][i]);
             VecN<T, PXV>::ld(src + dn_off, dn);
-#endif
         } else {
-#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
-            const uint32_t eb = ebuf_s + (uint32_t)((2 * (L - 1) + (P ^ 1)) * C::EDGE * (int)sizeof(T));
-            VecN<T, PXV>::lds(eb + (uint32_t)(e_up * (int)sizeof(T)), up);
-            VecN<T, PXV>::lds(eb + (uint32_t)(e_dn * (int)sizeof(T)), dn);
-#else
             const T* eb = ebuf + (size_t)(2 * (L - 1) + (P ^ 1)) * C::EDGE;
             VecN<T, PXV>::ld(eb + e_up, up);
             VecN<T, PXV>::ld(eb + e_dn, dn);
-#endif
         }
-        const T (&c)[PY][PXV] = *(L == 0 ? &R[P] : &O[L > 0 ? L - 1 : 0][P ^ 1]);
-        const T (&cm1)[PY][PXV] = *(L == 0 ? &R[P ^ 1] : &O[L > 0 ? L - 1 : 0][P]);
+        const T (&c)[PY][PXV] = *(L == 0 ? &R[HIST ? P : 0] : &O[L > 0 ? L - 1 : 0][HIST ? P ^ 1 : 0]);
+        const T (&cm1)[PY][PXV] = *(L == 0 ? &R[HIST ? P ^ 1 : 0] : &O[L > 0 ? L - 1 : 0][HIST ? P : 0]);
         const int pe = j - 2 * L - 1;  // local index of the plane being emitted
         const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
         if constexpr (L < K - 1) {
-            T (&o)[PY][PXV] = O[L][P];
+            T (&o)[PY][PXV] = O[L][HIST ? P : 0];
             t3_level<T, PXV, PY>(up, c, dn, cm1, lv[L], avg, o);
             if (!(upd && warp_all)) {
                 const unsigned m = upd ? mask : 0u;
+                // plane j-1 of the TMA ring (box, level 0): still there, the ring runs S-1 ahead
+                const T* prev = ring + (size_t)((j - 1) & (S - 1)) * C::PLANE + toff;
 #pragma unroll
                 for (int i = 0; i < PY; ++i)
 #pragma unroll
                     for (int k = 0; k < PXV; ++k)
-                        if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = cm1[i][k];
+                        if (!((m >> (i * PXV + k)) & 1u)) o[i][k] = HIST ? cm1[i][k] : prev[i * C::BX + k];
             }
-#if defined(SB200_T3_EXP) && (SB200_T3_EXP & 4)
-            const uint32_t wb = ebuf_s + (uint32_t)(((2 * L + P) * C::EDGE + e_own) * (int)sizeof(T));
-            VecN<T, PXV>::sts(wb, o[0]);
-            VecN<T, PXV>::sts(wb + (uint32_t)(C::BX * (int)sizeof(T)), o[PY - 1]);
-#else
             T* wb = ebuf + (size_t)(2 * L + P) * C::EDGE + e_own;
             VecN<T, PXV>::st(wb, o[0]);
             VecN<T, PXV>::st(wb + C::BX, o[PY - 1]);
-#endif
         } else {
             // The last level needs no pass-through fix-up: only updatable points of planes
             // inside the update domain are ever stored.  The box variant drops it (and with it
@@ -530,6 +541,18 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
 #pragma unroll
                 for (int i = 0; i < PY; ++i)
                     if (s_rows & (1u << i)) VecN<T, PXV>::st(sp + i * C::VX, o[i]);
+                if (x_tail) {
+                    // the TMA unit clips in 16-byte units, so the output map ends at the last
+                    // full 16 bytes of a row: the thread that owns the ragged end of the rows
+                    // (n[0] mod PXV points) stores it itself
+                    T* gp = out + g.idx(gx, gy, z_first + pe);
+#pragma unroll
+                    for (int i = 0; i < PY; ++i)
+                        if ((s_rows & (1u << i)) && gy + i < g.n[1])
+#pragma unroll
+                            for (int k = 0; k < PXV - 1; ++k)
+                                if (k < x_tail) gp[(long long)i * g.pitch_x + k] = o[i][k];
+                }
             }
         }
     };
@@ -560,17 +583,17 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         if (tid == 0) tma_store_wait_read();
         __syncthreads();
         if (tid == 0) {
-            if (storing)
+            if (storing && g.n[0] >= PXV)  // narrower grids are all "ragged end"
                 tma_store_3d(&omap, stage + (size_t)P * C::STAGE_BYTES, ox0, oy0,
 #ifdef SB200_PROBE_ZWRAP
                              oz0 + K + ((po - K) & (SB200_PROBE_ZWRAP - 1)));
 #else
                              oz0 + po);
 #endif
-            if (j + S < nin) {
-                const int st = j & (S - 1);
+            if (j + S - 1 < nin) {  // into the slot of plane j-1, which step j was the last to read
+                const int st = (j + S - 1) & (S - 1);
                 mbar_expect_tx(&bars[st], (uint32_t)C::PLANE_BYTES);
-                tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + T3_PROBE_Z(j + S));
+                tma_load_3d(ring + (size_t)st * C::PLANE, &tmap, &bars[st], cx, cy, cz0 + T3_PROBE_Z(j + S - 1));
             }
         }
     };

@@ -161,6 +161,33 @@ def test_tma3d_box27_kernel(gpu, n, T, k, dtype):
     assert t.kernel == capi.KERNEL_TMA3D and t.launches == -(-T // k)
 
 
+@pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
+@pytest.mark.parametrize("n,T,k,seed", [
+    ((1, 1, 1), 3, 2, 1), ((5, 4, 3), 3, 1, 1), ((60, 62, 20), 4, 2, 1), ((61, 59, 33), 3, 1, 2),
+    ((130, 70, 40), 9, 2, 3), ((123, 125, 64), 50, 2, 1), ((70, 66, 30), 6, 2, 0),
+])
+def test_tma3d_box27_reassociated_within_tolerance(gpu, n, T, k, seed, dtype, tol):
+    """SB200_FLAG_REASSOCIATE: the separable 27-point kernel (x, y, z partial sums) against the
+    reference-order oracle: max relative error <= 1e-12 (fp64) / 1e-5 (fp32) after T steps, the
+    north star's tolerance, with exact zeros where the oracle has exact zeros (seed 0 = the
+    reference init: zeros ahead of the diffusion front)."""
+    a, b = _oracle_pair(n, 1, dtype, seed)
+    ga, gb = a.copy(), b.copy()
+    want = b if oracle.sweep(n, 1, capi.BOX, T, a, b, threads=oracle.max_threads()) else a
+    got, t = sweep.run_host(n, ga, gb, T, radius=1, shape=capi.BOX, time_block=k, kernel=capi.KERNEL_TMA3D,
+                            flags=capi.FLAG_REASSOCIATE)
+    assert t.kernel == capi.KERNEL_TMA3D
+    w, g = want.astype(np.float64), got.astype(np.float64)
+    assert np.array_equal(w == 0, g == 0), "zero sets differ"
+    scale = np.maximum(np.abs(w), np.abs(g))
+    rel = np.abs(w - g)[scale > 0] / scale[scale > 0]
+    assert rel.size == 0 or rel.max() <= tol, f"max relative error {rel.max():.3e}"
+    # without the flag the same call is bit-exact
+    ga2, gb2 = _oracle_pair(n, 1, dtype, seed)
+    got2, _ = sweep.run_host(n, ga2, gb2, T, radius=1, shape=capi.BOX, time_block=k, kernel=capi.KERNEL_TMA3D)
+    assert np.array_equal(want.view(np.uint8), got2.view(np.uint8))
+
+
 def test_auto_dispatch(gpu):
     assert _check((200, 100), 1, capi.BOX, np.float32, 8).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70, 60), 1, capi.STAR, np.float64, 4).kernel == capi.KERNEL_TMA3D

@@ -19,10 +19,14 @@ CFG = {"c2": ((512, 512, 512), capi.STAR, capi.F64, 2, 48), "c2k1": ((512, 512, 
        "c2k3": ((512, 512, 512), capi.STAR, capi.F64, 3, 48),
        "c3": ((512, 512, 512), capi.BOX, capi.F64, 2, 24), "c3k1": ((512, 512, 512), capi.BOX, capi.F64, 1, 12),
        "c2f32": ((512, 512, 512), capi.STAR, capi.F32, 2, 48), "c3f32": ((512, 512, 512), capi.BOX, capi.F32, 2, 24),
-       "c5": ((1024, 1024, 256), capi.STAR, capi.F64, 2, 24)}
+       "c5": ((1024, 1024, 256), capi.STAR, capi.F64, 2, 24),
+       # SB200_FLAG_REASSOCIATE: separable 27-point sums (tolerance-level parity)
+       "c3sep": ((512, 512, 512), capi.BOX, capi.F64, 2, 24), "c3sepk1": ((512, 512, 512), capi.BOX, capi.F64, 1, 12),
+       "c3sepf32": ((512, 512, 512), capi.BOX, capi.F32, 2, 24)}
 for name in sys.argv[2:] or ["c2"]:
     n, shape, dtype, k, T = CFG[name]
-    d = capi.make_desc(n, 1, shape, dtype, T, time_block=k, kernel=capi.KERNEL_TMA3D)
+    d = capi.make_desc(n, 1, shape, dtype, T, time_block=k, kernel=capi.KERNEL_TMA3D,
+                       flags=capi.FLAG_REASSOCIATE if "sep" in name else 0)
     g = sweep.DeviceGrids(d)
     g.fill(capi.INIT_RANDOM, seed=1)
     g.sweep(2 * k)
