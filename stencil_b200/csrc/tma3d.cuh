@@ -492,19 +492,19 @@ sweep_tma3d_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             const T* src = ring + (size_t)st * C::PLANE + toff;
             VecN<T, PXV>::ld(src + up_off, up);
 #pragma unroll
-            for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[HIST ? P : 0][i]);
+            for (int i = 0; i < PY; ++i) VecN<T, PXV>::ld(src + i * C::BX, R[NS == 2 ? P : 0][i]);
             VecN<T, PXV>::ld(src + dn_off, dn);
         } else {
             const T* eb = ebuf + (size_t)(2 * (L - 1) + (P ^ 1)) * C::EDGE;
             VecN<T, PXV>::ld(eb + e_up, up);
             VecN<T, PXV>::ld(eb + e_dn, dn);
         }
-        const T (&c)[PY][PXV] = *(L == 0 ? &R[HIST ? P : 0] : &O[L > 0 ? L - 1 : 0][HIST ? P ^ 1 : 0]);
-        const T (&cm1)[PY][PXV] = *(L == 0 ? &R[HIST ? P ^ 1 : 0] : &O[L > 0 ? L - 1 : 0][HIST ? P : 0]);
+        const T (&c)[PY][PXV] = *(L == 0 ? &R[NS == 2 ? P : 0] : &O[L > 0 ? L - 1 : 0][NS == 2 ? P ^ 1 : 0]);
+        const T (&cm1)[PY][PXV] = *(L == 0 ? &R[NS == 2 ? P ^ 1 : 0] : &O[L > 0 ? L - 1 : 0][NS == 2 ? P : 0]);
         const int pe = j - 2 * L - 1;  // local index of the plane being emitted
         const bool upd = pe >= p_dom_lo && pe < p_dom_hi;
         if constexpr (L < K - 1) {
-            T (&o)[PY][PXV] = O[L][HIST ? P : 0];
+            T (&o)[PY][PXV] = O[L][NS == 2 ? P : 0];
             t3_level<T, PXV, PY>(up, c, dn, cm1, lv[L], avg, o);
             if (!(upd && warp_all)) {
                 const unsigned m = upd ? mask : 0u;
