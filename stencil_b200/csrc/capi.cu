@@ -377,7 +377,8 @@ struct Choice {
 
 // WARP2D family: radius 1 star/box (warp2d.cuh), radius 2..4 star (warp2dr.cuh).
 bool warp2d_supports(const sb200_desc* d) {
-    return d->ndim == 2 && (d->radius == 1 || (d->shape == SB200_STAR && d->radius >= 2 && d->radius <= 4));
+    return d->ndim == 2 && (d->radius == 1 || (d->shape == SB200_STAR && d->radius >= 2 && d->radius <= 4) ||
+                            (d->shape == SB200_BOX && d->radius == 2));
 }
 
 Choice choose(const sb200_desc* d) {
@@ -389,7 +390,9 @@ Choice choose(const sb200_desc* d) {
     if (kern == SB200_KERNEL_AUTO)
         kern = w2d_ok ? SB200_KERNEL_WARP2D : t3_ok ? SB200_KERNEL_TMA3D : l1_ok ? SB200_KERNEL_LINE1D : SB200_KERNEL_GENERIC;
     c.kernel = kern;
-    c.max_k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? w2r_max_k((int)d->radius, (int)esize(d->dtype)) : W2D_MAXK)
+    c.max_k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? (d->shape == SB200_BOX ? w2r_box_max_k((int)d->radius, (int)esize(d->dtype))
+                                                                                     : w2r_max_k((int)d->radius, (int)esize(d->dtype)))
+                                                           : W2D_MAXK)
               : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
               : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30)
               : kern == SB200_KERNEL_LINE1D ? L1D_MAXK : 1;
@@ -403,7 +406,7 @@ Choice choose(const sb200_desc* d) {
 
 int check_choice(const sb200_desc* d, const Choice& c) {
     if (c.kernel == SB200_KERNEL_WARP2D && !warp2d_supports(d))
-        return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2 and radius=1 (star or box) or radius 2..4 (star)");
+        return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2 and radius=1 (star or box), radius 2..4 (star) or radius 2 (box)");
     if (c.kernel == SB200_KERNEL_LINE1D && !(d->ndim == 1 && d->radius <= 4))
         return fail(SB200_ERR_UNSUPPORTED, "LINE1D kernel needs ndim=1, radius 1..4");
     if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
@@ -436,7 +439,7 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_WARP2D:
             if (g.r > 1)
-                CU_TRY(launch_warp2dr<T>(a, b, g, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
+                CU_TRY(launch_warp2dr<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             else
                 CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             return SB200_OK;

@@ -67,13 +67,62 @@ template <class T, int R> struct W2rLevel {
     }
 };
 
-template <class T, int R, int K, bool EDGE>
+// ---- box of radius R (25-point for R = 2) ------------------------------------------------------
+// Oracle order: one chain from 0 over dy ascending (outer) and dx ascending
+// (inner), then one multiply.  An arriving row y is row dy = y - y' of the 2R+1 open outputs
+// y' = y-R .. y+R, so 2R+1 accumulator chains advance by its 2R+1 window values each; output
+// y-R completes and output y+R opens in the same slot (slots = row index mod 2R).  Same lag of
+// R rows per level as the star, so the streaming code is shared.
+__host__ __device__ constexpr int w2r_box_max_k(int R, int elem_size) { return R == 2 ? (elem_size == 4 ? 2 : 1) : 0; }
+
+template <class T, int R> struct W2rBoxLevel {
+    static constexpr int PHASES = 2 * R;
+    T prev[R][4];       // the last R input rows (pass-through values of the rows still to be emitted)
+    T pend[2 * R][4];   // open accumulator chains
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int s = 0; s < R; ++s) prev[s][i] = T(0);
+#pragma unroll
+            for (int s = 0; s < 2 * R; ++s) pend[s][i] = T(0);
+        }
+    }
+    template <int P, bool EDGE>
+    __device__ __forceinline__ void step(const T (&w)[4 + 2 * R], T avg, unsigned upd, Row4<T>& o) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            auto chain = [&](T acc) {
+#pragma unroll
+                for (int k = 0; k <= 2 * R; ++k) acc = add_rn(acc, w[i + k]);
+                return acc;
+            };
+            constexpr int SL = (P + R) % (2 * R);  // slot shared by the completing and the opening output
+            const T f = mul_rn(chain(pend[SL][i]), avg);
+            o.v[i] = (!EDGE || ((upd >> i) & 1u)) ? f : prev[P % R][i];
+            pend[SL][i] = chain(T(0));
+#pragma unroll
+            for (int d = -R + 1; d <= R - 1; ++d) {
+                const int sl = (P + d + 2 * R) % (2 * R);
+                pend[sl][i] = chain(pend[sl][i]);
+            }
+            prev[P % R][i] = w[R + i];
+        }
+    }
+};
+
+template <class T, int R, int SHAPE> struct W2rLevelSel { using type = W2rLevel<T, R>; static constexpr int PHASES = R; };
+template <class T, int R> struct W2rLevelSel<T, R, BOX> { using type = W2rBoxLevel<T, R>; static constexpr int PHASES = 2 * R; };
+
+template <class T, int R, int K, bool EDGE, int SHAPE = STAR>
 __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restrict__ dst, long long pitch,
                                            int nsteps, int j_dom_lo, int j_dom_hi, int j_row_lo,
                                            int j_row_hi, unsigned mxmask, T* ring, bool lane_valid,
                                            int ncols_valid, T avg) {
     constexpr int D = w2r_depth(R);
-    W2rLevel<T, R> lv[K];
+    constexpr int PH = W2rLevelSel<T, R, SHAPE>::PHASES;
+    static_assert(D % PH == 0 && PH <= 4, "the row loop is unrolled by a multiple of the phase count");
+    typename W2rLevelSel<T, R, SHAPE>::type lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
     // unconditional, clamped loads (see warp2d.cuh): rows outside the allocation or past the
@@ -115,11 +164,11 @@ __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restr
 #pragma unroll
                 for (int i = 0; i < 4; ++i) w[R + i] = cur.v[i];
                 Row4<T> o;
-                switch (d % R) {  // compile-time after unrolling
+                switch (d % PH) {  // compile-time after unrolling
                     case 0: lv[l].template step<0, EDGE>(w, avg, upd, o); break;
-                    case 1: lv[l].template step<1 % R, EDGE>(w, avg, upd, o); break;
-                    case 2: lv[l].template step<2 % R, EDGE>(w, avg, upd, o); break;
-                    default: lv[l].template step<3 % R, EDGE>(w, avg, upd, o); break;
+                    case 1: lv[l].template step<1 % PH, EDGE>(w, avg, upd, o); break;
+                    case 2: lv[l].template step<2 % PH, EDGE>(w, avg, upd, o); break;
+                    default: lv[l].template step<3 % PH, EDGE>(w, avg, upd, o); break;
                 }
                 cur = o;
             }
@@ -139,7 +188,7 @@ __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restr
 
 // in -> out, K fused steps of the radius-R star, output rows [ob, oe) (slab-interior
 // coordinates).  Work item = (x strip, y chunk), one per warp, as in sweep_warp2d_kernel.
-template <class T, int R, int K>
+template <class T, int R, int K, int SHAPE = STAR>
 __global__ void __launch_bounds__(32 * W2D_WARPS)
 sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domain dom,
                      long long ob, long long oe, int nstrips, int chunk_rows, long long nitems,
@@ -185,30 +234,38 @@ sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Doma
     const bool interior =
         __all_sync(0xffffffffu, mxmask == 0xFu) && j_dom_lo <= -K * R && j_dom_hi >= nsteps;
     if (interior) {
-        w2r_stream<T, R, K, false>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
+        w2r_stream<T, R, K, false, SHAPE>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
                                    mxmask, ring, lane_valid, ncols_valid, avg);
     } else {
-        w2r_stream<T, R, K, true>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
+        w2r_stream<T, R, K, true, SHAPE>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
                                   mxmask, ring, lane_valid, ncols_valid, avg);
     }
 }
 
-template <class T, int R, int K>
+template <class T, int R, int K, int SHAPE = STAR>
 static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
                                     long long oe, const Tuning& tn, cudaStream_t st) {
     if (oe <= ob) return cudaSuccess;
     const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, R, tn.prefer_chunk);
-    const T avg = Avg<T>::value(STAR, 2, R);
+    const T avg = Avg<T>::value(SHAPE, 2, R);
     const unsigned blocks = (unsigned)((p.nitems + W2D_WARPS - 1) / W2D_WARPS);
-    sweep_warp2dr_kernel<T, R, K><<<blocks, 32 * W2D_WARPS, 0, st>>>(
+    sweep_warp2dr_kernel<T, R, K, SHAPE><<<blocks, 32 * W2D_WARPS, 0, st>>>(
         in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, p.nitems, avg);
     return cudaGetLastError();
 }
 
-// 2-D star, radius 2..4, K fused steps (1 .. w2r_max_k(R, sizeof(T))).
+// 2-D star, radius 2..4, K fused steps (1 .. w2r_max_k(R, sizeof(T))); 2-D box, radius 2
+// (25-point), K fused steps (1 .. w2r_box_max_k).
 template <class T>
-static cudaError_t launch_warp2dr(const T* in, T* out, const Grid& g, Domain dom, int K, long long ob,
+static cudaError_t launch_warp2dr(const T* in, T* out, const Grid& g, int shape, Domain dom, int K, long long ob,
                                   long long oe, const Tuning& tn, cudaStream_t st) {
+    if (shape == BOX) {
+        if (g.r != 2 || K < 1 || K > w2r_box_max_k(2, (int)sizeof(T))) return cudaErrorInvalidValue;
+        if (K == 1) return launch_warp2dr_k<T, 2, 1, BOX>(in, out, g, dom, ob, oe, tn, st);
+        if constexpr (w2r_box_max_k(2, (int)sizeof(T)) >= 2)
+            return launch_warp2dr_k<T, 2, 2, BOX>(in, out, g, dom, ob, oe, tn, st);
+        return cudaErrorInvalidValue;
+    }
     if (K < 1 || g.r < 2 || g.r > 4 || K > w2r_max_k(g.r, (int)sizeof(T))) return cudaErrorInvalidValue;
 #define SB200_W2R(RR, KK) \
     if constexpr (KK <= w2r_max_k(RR, (int)sizeof(T))) \

@@ -33,7 +33,7 @@ def resolve_kernel(desc: capi.Desc):
     """(family, fused depth) the library will use for this descriptor (mirrors choose()
     in csrc/capi.cu; max depth is asked from the library)."""
     star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
-    w2d = desc.ndim == 2 and (desc.radius == 1 or star_r)
+    w2d = desc.ndim == 2 and (desc.radius == 1 or star_r or (desc.shape == capi.BOX and desc.radius == 2))
     t3 = desc.ndim == 3 and desc.radius == 1
     l1 = desc.ndim == 1 and desc.radius <= 4
     kern = desc.kernel

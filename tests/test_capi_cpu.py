@@ -98,7 +98,11 @@ def test_plan_host_logic(monkeypatch):
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 4, 25)  # radius-2 star: fused warp kernel
     p = capi.plan(capi.make_desc((400, 400), 4, capi.STAR, capi.F64, 100), 100)
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 1, 100)
-    assert capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    p = capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F32, 100), 100)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 2, 50)   # 25-point box: fused warp kernel
+    p = capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F64, 100), 100)
+    assert (p.kernel, p.time_block) == (capi.KERNEL_WARP2D, 1)
+    assert capi.plan(capi.make_desc((400, 400), 3, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     assert capi.plan(capi.make_desc((400, 400), 5, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     # 1-D: warp segments of 512 points; 16 fused steps by default at r=1 (10 here: one launch,
     # 512 - 12 - 10 -> 488 stored per segment), 8 at r=4

@@ -1,10 +1,11 @@
 """Parity at BASELINE.json's FULL sizes (-m gpu).
 
-Configs 1-3 and config 4 at T=100 are compared with the CPU oracle directly (order-
-independent 64-bit checksum of bit patterns + global index: equal checksums mean every
-point is bit-identical); the oracle needs a few seconds per case on the box's host cores.
-Where the oracle would take minutes (config 4 at T=1000) or tens of GB of host memory
-(config 5), size-independent properties take over: the result must not depend on the fused
+Configs 1-4 are compared with the CPU oracle directly (order-independent 64-bit checksum of
+bit patterns + global index: equal checksums mean every point is bit-identical); the oracle
+needs a few seconds per case on the box's host cores, config 4 at its full T = 1000 about
+75 s.  Where the oracle would need tens of GB of host memory (config 5: covered at N = 1, 2,
+4, 8 by bench.py's config5 leg against a committed 1-GPU checksum, and through the C++ CLI
+with -c at 8 GPUs), size-independent properties take over: the result must not depend on the fused
 depth k nor on the kernel family, because every kernel keeps the oracle's summation order."""
 import numpy as np
 import pytest
@@ -44,6 +45,14 @@ def _oracle_checksum(n, shape, dtype, T, seed=1):
 ])
 def test_full_size_matches_oracle(gpu, name, n, shape, dtype, T):
     assert _gpu_checksum(n, shape, dtype, T) == _oracle_checksum(n, shape, dtype, T), name
+
+
+def test_config4_full_T_matches_oracle(gpu):
+    """BASELINE configs[3] exactly as written — 16384^2 fp32 9-point box, T = 1000 — against the
+    CPU oracle, every point (268 G updates: about 75 s on 16 host threads; the slow test of the
+    suite)."""
+    n, T = (16384, 16384), 1000
+    assert _gpu_checksum(n, capi.BOX, capi.F32, T) == _oracle_checksum(n, capi.BOX, capi.F32, T)
 
 
 def test_config4_full_T_is_independent_of_fused_depth(gpu):

@@ -135,9 +135,23 @@ def test_line1d_kernel(gpu, n, r, T, k, shape, dtype):
     assert t.kernel == capi.KERNEL_LINE1D and t.time_block == ke and t.launches == -(-T // ke)
 
 
-def test_warp2d_radius_box_is_unsupported(gpu):
-    d = capi.make_desc((64, 64), radius=2, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
-    a = np.zeros((68, 68), np.float32)
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,T,k", [
+    ((1, 1), 3, 2), ((3, 2), 5, 1), ((120, 50), 4, 2), ((121, 97), 9, 2), ((250, 31), 7, 1),
+    ((1000, 129), 11, 2), ((113, 113), 8, 1), ((119, 200), 7, 2), ((64, 2000), 5, 2),
+])
+def test_warp2d_radius2_box_kernel(gpu, n, T, k, dtype):
+    """25-point box (radius 2) through the fused warp kernel: 2R+1 accumulator chains per level,
+    each in the oracle's order; bit-exact."""
+    kmax = 2 if dtype == np.float32 else 1
+    t = _check(n, 2, capi.BOX, dtype, T, time_block=k, kernel=capi.KERNEL_WARP2D)
+    ke = min(k, kmax)
+    assert t.kernel == capi.KERNEL_WARP2D and t.time_block == ke and t.launches == -(-T // ke)
+
+
+def test_warp2d_radius3_box_is_unsupported(gpu):
+    d = capi.make_desc((64, 64), radius=3, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
+    a = np.zeros((70, 70), np.float32)
     assert capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, a.ctypes.data, None) == capi.ERR_UNSUPPORTED
 
 
@@ -195,7 +209,8 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
-    assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_WARP2D
+    assert _check((80, 70), 3, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 5, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
     assert _check((3000,), 2, capi.BOX, np.float64, 9).kernel == capi.KERNEL_LINE1D
     assert _check((3000,), 6, capi.STAR, np.float32, 3).kernel == capi.KERNEL_GENERIC

@@ -72,6 +72,13 @@ if "rad" in which:  # general-radius 2-D star: fused warp kernel vs the one-thre
                         capi.make_desc((8192, 8192), r, capi.STAR, dt, 24, kernel=capi.KERNEL_WARP2D))):
                     run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 24, capi.KERNEL_WARP2D, k, r=r)
             run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 8, capi.KERNEL_GENERIC, 1, r=r)
+if "box2" in which:  # 25-point box: fused warp kernel vs one launch per step
+    for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
+        for k in (1, 2):
+            if k <= capi.lib().sb200_max_time_block(ctypes.byref(
+                    capi.make_desc((8192, 8192), 2, capi.BOX, dt, 24, kernel=capi.KERNEL_WARP2D))):
+                run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 24, capi.KERNEL_WARP2D, k, r=2)
+        run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 8, capi.KERNEL_GENERIC, 1, r=2)
 if "line" in which:  # 1-D: fused register kernel vs one launch per step
     for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
         for r in (1, 4):
