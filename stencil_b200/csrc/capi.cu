@@ -24,6 +24,7 @@
 #include "generic.cuh"
 #include "resident2d_api.h"
 #include "tma3d.cuh"
+#include "tma3dr.cuh"
 #include "util_kernels.cuh"
 #include "warp2d.cuh"
 #include "warp2dr.cuh"
@@ -368,6 +369,25 @@ int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domai
     }
 }
 
+// 3-D star of radius 2 (13-point), one step per launch (tma3dr.cuh).
+template <class T>
+int launch_tma3dr(const T* in, T* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
+                  int prefer_chunk) {
+    using C = T3R<T, 2>;
+    if (oe <= ob) return SB200_OK;
+    if (int rc = set_smem_attr_once(sweep_tma3dr_kernel<T, 2>, C::SMEM)) return rc;
+    const CUtensorMap* mp = nullptr;
+    if (int rc = get_tensor_map(in, dtype, g, C::BX, C::BY, false, &mp)) return rc;
+    const CUtensorMap imap = *mp;
+    if (int rc = get_tensor_map(out, dtype, g, C::VX, C::VY, true, &mp)) return rc;
+    const CUtensorMap omap = *mp;
+    const T3Plan p = t3r_plan<T, 2>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
+    sweep_tma3dr_kernel<T, 2><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
+        imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2));
+    CU_TRY(cudaGetLastError());
+    return SB200_OK;
+}
+
 // Kernel family + fused depth for a descriptor.
 struct Choice {
     int kernel;
@@ -381,10 +401,15 @@ bool warp2d_supports(const sb200_desc* d) {
                             (d->shape == SB200_BOX && d->radius == 2));
 }
 
+// TMA3D family: radius 1 star / box (tma3d.cuh), radius 2 star (tma3dr.cuh).
+bool tma3d_supports(const sb200_desc* d) {
+    return d->ndim == 3 && (d->radius == 1 || (d->radius == 2 && d->shape == SB200_STAR));
+}
+
 Choice choose(const sb200_desc* d) {
     Choice c;
     const bool w2d_ok = warp2d_supports(d);
-    const bool t3_ok = d->ndim == 3 && d->radius == 1;
+    const bool t3_ok = tma3d_supports(d);
     const bool l1_ok = d->ndim == 1 && d->radius <= 4;
     int kern = d->kernel;
     if (kern == SB200_KERNEL_AUTO)
@@ -393,7 +418,7 @@ Choice choose(const sb200_desc* d) {
     c.max_k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? (d->shape == SB200_BOX ? w2r_box_max_k((int)d->radius, (int)esize(d->dtype))
                                                                                      : w2r_max_k((int)d->radius, (int)esize(d->dtype)))
                                                            : W2D_MAXK)
-              : kern == SB200_KERNEL_TMA3D ? (d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
+              : kern == SB200_KERNEL_TMA3D ? (d->radius > 1 ? 1 : d->shape == SB200_BOX ? T3_MAXK_BOX : T3_MAXK)
               : kern == SB200_KERNEL_RESIDENT2D ? (1 << 30)
               : kern == SB200_KERNEL_LINE1D ? L1D_MAXK : 1;
     int k = (int)d->time_block;
@@ -409,8 +434,8 @@ int check_choice(const sb200_desc* d, const Choice& c) {
         return fail(SB200_ERR_UNSUPPORTED, "WARP2D kernel needs ndim=2 and radius=1 (star or box), radius 2..4 (star) or radius 2 (box)");
     if (c.kernel == SB200_KERNEL_LINE1D && !(d->ndim == 1 && d->radius <= 4))
         return fail(SB200_ERR_UNSUPPORTED, "LINE1D kernel needs ndim=1, radius 1..4");
-    if (c.kernel == SB200_KERNEL_TMA3D && !(d->ndim == 3 && d->radius == 1))
-        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3, radius=1");
+    if (c.kernel == SB200_KERNEL_TMA3D && !tma3d_supports(d))
+        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3 and radius=1 (star or box) or radius=2 (star)");
     if (c.kernel == SB200_KERNEL_RESIDENT2D &&
         !(d->ndim == 2 && d->radius == 1 && resident2d_fits((long long)d->n[0], (long long)d->n[1], (int)esize(d->dtype))))
         return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel needs ndim=2, radius=1 and a grid that fits one "
@@ -444,6 +469,10 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
                 CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
+            if (g.r > 1) {
+                if (k != 1) return fail(SB200_ERR_INVALID, "the radius-2 TMA3D kernel fuses 1 step");
+                return launch_tma3dr<T>(a, b, d->dtype, g, ob, oe, st, tile_pref(d));
+            }
             return launch_tma3d<T>(a, b, d->dtype, g, t3_shape(d),
                                    dom, k, ob, oe, st, kNoLink, tile_pref(d));
         case SB200_KERNEL_LINE1D:
@@ -625,6 +654,13 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
         info->tiles_y = 1;
         info->chunks = (uint32_t)p.nchunks;
         info->chunk_extent = (uint32_t)p.chunk_rows;
+    } else if (c.kernel == SB200_KERNEL_TMA3D && desc->radius > 1) {
+        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                                                  : t3r_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
+        info->tiles_x = (uint32_t)p.ntx;
+        info->tiles_y = (uint32_t)p.nty;
+        info->chunks = (uint32_t)p.nchunks;
+        info->chunk_extent = (uint32_t)p.chunk_planes;
     } else if (c.kernel == SB200_KERNEL_TMA3D) {
         T3Plan p;
         if (desc->dtype == SB200_F64)
@@ -767,8 +803,8 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     if (int rc = ensure_ready()) return rc;
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
-    if (c.kernel != SB200_KERNEL_TMA3D)
-        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D family (3-D, radius 1)");
+    if (c.kernel != SB200_KERNEL_TMA3D || desc->radius != 1)
+        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D family at radius 1");
     if (steps < 1 || (int)steps > c.max_k)
         return fail(SB200_ERR_INVALID, "linked sweep fuses 1..%d steps (got %u)", c.max_k, steps);
     const Grid g = make_grid(desc, ghost);

@@ -653,15 +653,14 @@ struct T3Plan {
     long long nchunks, blocks;
 };
 
-// Chunk count along z.  Every CTA streams its chunk plus 3K-1 pipeline planes, CTAs are
-// dispatched in blockIdx order to the first free SM (1 CTA per SM): pick the chunk count
-// with the smallest simulated makespan (in plane-steps).
-template <class T, int K>
-static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count, int prefer_planes = 0) {
-    using C = T3<T, K>;
+// Chunk count along z.  Every CTA streams its chunk plus `fill` pipeline planes (3K-1 for the
+// radius-1 kernels), CTAs are dispatched in blockIdx order to the first free SM: pick the chunk
+// count with the smallest simulated makespan (in plane-steps).
+static inline T3Plan t3_plan_core(long long nx, long long ny, long long planes, int sm_slots, int vx, int vy,
+                                  int fill, long long variant, int prefer_planes) {
     T3Plan p;
-    p.ntx = (int)((nx + C::VX - 1) / C::VX);
-    p.nty = (int)((ny + C::VY - 1) / C::VY);
+    p.ntx = (int)((nx + vx - 1) / vx);
+    p.nty = (int)((ny + vy - 1) / vy);
     const long long tiles = (long long)p.ntx * p.nty;
     if (prefer_planes > 0) {  // the caller's tile preference wins over the makespan search
         p.chunk_planes = (int)(prefer_planes < planes ? prefer_planes : planes);
@@ -669,11 +668,11 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
         p.blocks = tiles * p.nchunks;
         return p;
     }
-    // one cache per instantiation, shared by every host thread (slab workers, planners)
+    // one cache shared by every host thread (slab workers, planners)
     static std::map<std::array<long long, 6>, std::pair<int, long long>> cache;
     static std::mutex cache_mu;
     std::lock_guard<std::mutex> cache_lock(cache_mu);
-    const std::array<long long, 6> key = {nx, ny, planes, sm_count, K, (long long)sizeof(T)};
+    const std::array<long long, 6> key = {tiles, planes, sm_slots, fill, variant, 0};
     auto it = cache.find(key);
     if (it == cache.end()) {
         const double startup = 3.0;  // CTA launch + first TMA round trip, in plane-steps
@@ -687,10 +686,10 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
             if (c > 1 && nc == (planes + (planes + c - 2) / (c - 1) - 1) / ((planes + c - 2) / (c - 1)) &&
                 cp == (planes + c - 2) / (c - 1))
                 continue;  // same split as the previous candidate
-            const double dfull = cp + 3 * K - 1 + startup;
-            const double dlast = (planes - (nc - 1) * cp) + 3 * K - 1 + startup;
+            const double dfull = cp + fill + startup;
+            const double dlast = (planes - (nc - 1) * cp) + fill + startup;
             // min-heap of SM free times
-            heap.assign((size_t)sm_count * C::CTAS_PER_SM, 0.0);
+            heap.assign((size_t)sm_slots, 0.0);
             auto push_cta = [&](double d) {
                 std::pop_heap(heap.begin(), heap.end(), std::greater<double>());
                 heap.back() += d;
@@ -712,6 +711,12 @@ static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count
     p.nchunks = it->second.second;
     p.blocks = tiles * p.nchunks;
     return p;
+}
+
+template <class T, int K>
+static T3Plan t3_plan(long long nx, long long ny, long long planes, int sm_count, int prefer_planes = 0) {
+    using C = T3<T, K>;
+    return t3_plan_core(nx, ny, planes, sm_count * C::CTAS_PER_SM, C::VX, C::VY, 3 * K - 1, 0, prefer_planes);
 }
 
 }  // namespace sb200

@@ -34,7 +34,7 @@ def resolve_kernel(desc: capi.Desc):
     in csrc/capi.cu; max depth is asked from the library)."""
     star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
     w2d = desc.ndim == 2 and (desc.radius == 1 or star_r or (desc.shape == capi.BOX and desc.radius == 2))
-    t3 = desc.ndim == 3 and desc.radius == 1
+    t3 = desc.ndim == 3 and (desc.radius == 1 or (desc.radius == 2 and desc.shape == capi.STAR))
     l1 = desc.ndim == 1 and desc.radius <= 4
     kern = desc.kernel
     if kern == capi.KERNEL_AUTO:
@@ -240,10 +240,10 @@ class SlabSweep:
                              f"({self.ghost} each); use fewer ranks or a smaller time block")
         auto = exchange == "auto"
         if auto:
-            exchange = "p2p" if (world > 1 and self.kernel == capi.KERNEL_TMA3D) else "nccl"
+            exchange = "p2p" if (world > 1 and self.kernel == capi.KERNEL_TMA3D and self.r == 1) else "nccl"
         if exchange not in ("p2p", "nccl"):
             raise ValueError(f"exchange must be 'auto', 'p2p' or 'nccl' (got {exchange!r})")
-        if exchange == "p2p" and self.kernel != capi.KERNEL_TMA3D:
+        if exchange == "p2p" and (self.kernel != capi.KERNEL_TMA3D or self.r != 1):
             raise ValueError("exchange='p2p' needs the 3-D radius-1 kernel family")
         self.exchange = exchange if world > 1 else "none"
         p2p = self.exchange == "p2p"

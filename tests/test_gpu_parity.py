@@ -176,6 +176,18 @@ def test_tma3d_box27_kernel(gpu, n, T, k, dtype):
     assert t.kernel == capi.KERNEL_TMA3D and t.launches == -(-T // k)
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,T", [
+    ((1, 1, 1), 3), ((5, 4, 3), 4), ((60, 60, 20), 3), ((61, 59, 33), 5), ((130, 70, 40), 2),
+    ((200, 130, 17), 3), ((123, 125, 64), 4), ((300, 64, 9), 2), ((57, 121, 5), 1),
+])
+def test_tma3d_radius2_star_kernel(gpu, n, T, dtype):
+    """13-point star (3-D radius 2) through the TMA kernel (z history in registers), bit-exact."""
+    t = _check(n, 2, capi.STAR, dtype, T, kernel=capi.KERNEL_TMA3D)
+    assert t.kernel == capi.KERNEL_TMA3D and t.time_block == 1 and t.launches == T
+    assert _check(n, 2, capi.STAR, dtype, T).kernel == capi.KERNEL_TMA3D   # AUTO picks it
+
+
 @pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
 @pytest.mark.parametrize("n,T,k,seed", [
     ((1, 1, 1), 3, 2, 1), ((5, 4, 3), 3, 1, 1), ((60, 62, 20), 4, 2, 1), ((61, 59, 33), 3, 1, 2),
@@ -208,6 +220,8 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70, 60), 1, capi.STAR, np.float64, 4).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70, 20), 2, capi.STAR, np.float64, 2).kernel == capi.KERNEL_TMA3D
+    assert _check((80, 70, 20), 3, capi.STAR, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 3, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
@@ -230,7 +244,7 @@ def test_zero_iterations_is_identity(gpu):
 
 
 def test_unsupported_kernel_request_is_an_error(gpu):
-    d = capi.make_desc((8, 8, 8), radius=2, kernel=capi.KERNEL_TMA3D)
+    d = capi.make_desc((8, 8, 8), radius=2, shape=capi.BOX, kernel=capi.KERNEL_TMA3D)   # 125-point: generic only
     a = np.zeros((12, 12, 12), np.float32)
     rc = capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, a.ctypes.data, None)
     assert rc == capi.ERR_UNSUPPORTED
