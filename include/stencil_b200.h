@@ -227,6 +227,26 @@ int sb200_download(const sb200_desc* desc, uint32_t ghost, const void* dev, void
 int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* grid,
                           uint64_t z_offset, uint64_t z_total, void* stream, uint64_t* out);
 
+/* The same digest as sb200_checksum_device for callers that cannot allocate (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  The call performs no cudaMalloc /
+ * cudaFree and calls no allocating library routine: its scratch (one partial sum per block, a
+ * ticket and the result) is a file-scope `static __device__` array of
+ * 8 * (32 + SB200_NOALLOC_MAX_BLOCKS) = 65 792 bytes that every GPU loading the library holds
+ * until the process exits.  Limits and rules:
+ *   - at most SB200_NOALLOC_MAX_BLOCKS * SB200_NOALLOC_POINTS_PER_BLOCK = 134 217 728 interior
+ *     points per call (512^3); larger grids are rejected with SB200_ERR_INVALID;
+ *   - the library must already be bound to a device (sb200_init / sb200_init_multi): binding
+ *     allocates, so this call returns SB200_ERR_INVALID instead of doing it;
+ *   - every call shares the one array (it keeps the last call's contents; the call clears what
+ *     must start at zero): calls that OVERLAP on the GPU — different streams, different host
+ *     threads' streams — race on it.  Issue them one after another.
+ * Same arguments and result as sb200_checksum_device; the caller passes the grid.  Blocking. */
+#define SB200_NOALLOC_MAX_BLOCKS 8192
+#define SB200_NOALLOC_POINTS_PER_BLOCK 16384
+int sb200_checksum_device_noalloc(const sb200_desc* desc, uint32_t ghost, const void* grid,
+                                  uint64_t z_offset, uint64_t z_total, void* stream, uint64_t* out);
+
 /* Pinned host memory for callers that want full-speed PCIe copies in sb200_run_host. */
 int sb200_host_alloc(void** ptr, size_t bytes);
 int sb200_host_free(void* ptr);

@@ -29,7 +29,9 @@ SYMBOLS = [
     "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
     "sb200_init_multi", "sb200_group_size", "sb200_prepare", "sb200_slab_plan_for",
     "sb200_pipeline_schedule_slab", "sb200_link_reset", "sb200_host_alloc_for", "sb200_host_place",
+    "sb200_checksum_device_noalloc",
 ]
+NOALLOC_MAX_POINTS = 8192 * 16384
 MAX_GPUS = 16
 FLAG_REASSOCIATE = 1
 FLAG_BLOCK_TILE = 2
@@ -139,6 +141,7 @@ def lib() -> ctypes.CDLL:
         L.sb200_upload.argtypes = [dp, u32, vp, vp, vp]
         L.sb200_download.argtypes = [dp, u32, vp, vp, vp]
         L.sb200_checksum_device.argtypes = [dp, u32, vp, u64, u64, vp, ctypes.POINTER(u64)]
+        L.sb200_checksum_device_noalloc.argtypes = [dp, u32, vp, u64, u64, vp, ctypes.POINTER(u64)]
         L.sb200_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_size_t]
         L.sb200_host_free.argtypes = [vp]
         L.sb200_host_alloc_for.argtypes = [dp, ctypes.POINTER(vp), ctypes.POINTER(i32)]

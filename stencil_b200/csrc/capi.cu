@@ -97,6 +97,7 @@ struct State {
     int sm_count = 0;
     std::vector<MapEntry> maps;
     std::vector<const void*> attr_done;  // kernels whose launch attributes are set on this device
+    unsigned long long* noalloc_scratch = nullptr;  // device address of g_noalloc_scratch on this device
     // cached device buffers of sb200_run_host
     void* buf[2] = {nullptr, nullptr};
     size_t buf_bytes = 0;
@@ -550,6 +551,67 @@ int sweep_impl(const sb200_desc* d, uint32_t ghost, int lo_b, int hi_b, void* a,
 }
 
 }  // namespace
+
+// ---- no-allocation checksum (sb200_checksum_device_noalloc) ---------------------------------
+// Scratch of the variant below: a file-scope array in device memory, so the entry point never
+// allocates.  Every GPU that loads the library holds these 65 792 bytes until the process
+// exits.  Layout in 64-bit words: [0] ticket of the last-block election, [1] the result,
+// [32 ..) one partial sum per block.  In HOST code this name is only a stand-in for the symbol,
+// not a device address: the launcher resolves it with cudaGetSymbolAddress once per device.
+constexpr int NOALLOC_HEADER_WORDS = 32;  // keeps the partials 256-byte aligned
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_HEADER_WORDS + SB200_NOALLOC_MAX_BLOCKS];
+
+// Same digest as checksum_kernel (util_kernels.cuh), computed without atomics on the data:
+// block b sums the points [b * span, (b+1) * span), stores ONE partial, and the block that
+// draws the last ticket adds the partials up in index order (deterministic), publishes the
+// result and puts the ticket back to zero for the next call.
+template <class T>
+__global__ void __launch_bounds__(256)
+checksum_noalloc_kernel(const T* __restrict__ grid, Grid g, long long gn0, long long gn1, long long off,
+                        long long span, unsigned long long* __restrict__ scratch) {
+    __shared__ unsigned long long warp_sum[8];
+    __shared__ bool is_last;
+    const long long total = g.n[0] * g.n[1] * g.n[2];
+    const long long lo = (long long)blockIdx.x * span;
+    const long long hi = lo + span < total ? lo + span : total;
+    uint64_t local = 0;
+    for (long long i = lo + threadIdx.x; i < hi; i += 256) {
+        const long long x = i % g.n[0];
+        const long long y = (i / g.n[0]) % g.n[1];
+        const long long z = i / (g.n[0] * g.n[1]);
+        long long gy = y, gz = z;
+        if (g.ndim == 3) gz += off;
+        if (g.ndim == 2) gy += off;
+        const uint64_t lin = ((uint64_t)gz * (uint64_t)gn1 + (uint64_t)gy) * (uint64_t)gn0 + (uint64_t)x;
+        local += mix64(Bits<T>::of(grid[g.idx(x, y, z)]) ^ mix64(lin));
+    }
+    auto block_sum = [&](uint64_t v) -> uint64_t {  // valid in thread 0
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        __syncthreads();  // warp_sum may still be read from the previous use
+        if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = v;
+        __syncthreads();
+        uint64_t t = 0;
+        if (threadIdx.x == 0)
+            for (int w = 0; w < 8; ++w) t += warp_sum[w];
+        return t;
+    };
+    const uint64_t mine = block_sum(local);
+    if (threadIdx.x == 0) {
+        scratch[NOALLOC_HEADER_WORDS + blockIdx.x] = mine;
+        __threadfence();
+        is_last = atomicAdd(&scratch[0], 1ull) == (unsigned long long)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    uint64_t acc = 0;
+    for (unsigned j = threadIdx.x; j < gridDim.x; j += 256) acc += __ldcg(&scratch[NOALLOC_HEADER_WORDS + j]);
+    const uint64_t all = block_sum(acc);
+    if (threadIdx.x == 0) {
+        scratch[1] = all;
+        scratch[0] = 0;
+    }
+}
 
 // ---------------------------------------------------------------------------------
 extern "C" {
@@ -1328,6 +1390,52 @@ int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* gr
     CU_TRY(cudaGetLastError());
     unsigned long long h = 0;
     CU_TRY(cudaMemcpyAsync(&h, DS().d_acc, sizeof h, cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    *out = (uint64_t)h;
+    return SB200_OK;
+}
+
+int sb200_checksum_device_noalloc(const sb200_desc* desc, uint32_t ghost, const void* grid, uint64_t z_offset,
+                                  uint64_t z_total, void* stream, uint64_t* out) {
+    if (int rc = validate(desc)) return rc;
+    if (!grid || !out) return fail(SB200_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    // binding a device allocates (context, streams): this entry point must not be the one to do it
+    if (!DS().ready)
+        return fail(SB200_ERR_INVALID, "sb200_checksum_device_noalloc allocates nothing: call sb200_init first");
+    if (desc->ndim == 1 && ghost) return fail(SB200_ERR_INVALID, "1-D grids cannot carry ghost cells");
+    const Grid g = make_grid(desc, ghost);
+    const long long total = g.n[0] * g.n[1] * g.n[2];
+    const long long span = SB200_NOALLOC_POINTS_PER_BLOCK;
+    const long long blocks = (total + span - 1) / span;
+    if (blocks > SB200_NOALLOC_MAX_BLOCKS)
+        return fail(SB200_ERR_INVALID,
+                    "grid of %lld points exceeds the no-allocation limit of %lld points (%d partial sums of %d "
+                    "points in the static scratch array); use sb200_checksum_device",
+                    total, (long long)SB200_NOALLOC_MAX_BLOCKS * span, SB200_NOALLOC_MAX_BLOCKS,
+                    SB200_NOALLOC_POINTS_PER_BLOCK);
+    State& D = DS();
+    CU_TRY(cudaSetDevice(D.device));
+    if (!D.noalloc_scratch) {
+        // once per device, with that device current: the device address behind the symbol
+        unsigned long long* p = nullptr;
+        CU_TRY(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) return fail(SB200_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        D.noalloc_scratch = p;
+    }
+    long long gn[3] = {g.n[0], g.n[1], g.n[2]};
+    if (z_total) gn[desc->ndim - 1] = (long long)z_total;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the previous call's contents: ticket and result start at zero; every
+    // partial this launch reads is written by it first
+    CU_TRY(cudaMemsetAsync(D.noalloc_scratch, 0, 2 * sizeof(unsigned long long), st));
+    if (desc->dtype == SB200_F64)
+        checksum_noalloc_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((const double*)grid, g, gn[0], gn[1], (long long)z_offset, span, D.noalloc_scratch);
+    else
+        checksum_noalloc_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)grid, g, gn[0], gn[1], (long long)z_offset, span, D.noalloc_scratch);
+    CU_TRY(cudaGetLastError());
+    unsigned long long h = 0;
+    CU_TRY(cudaMemcpyAsync(&h, D.noalloc_scratch + 1, sizeof h, cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
     *out = (uint64_t)h;
     return SB200_OK;
