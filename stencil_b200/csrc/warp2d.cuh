@@ -24,7 +24,7 @@ constexpr int W2D_PX = 4;                 // x points per lane
 constexpr int W2D_WIDTH = 32 * W2D_PX;    // strip width incl. halo
 constexpr int W2D_WARPS = 4;              // warps (independent strips) per block
 constexpr int W2D_DEPTH = 8;              // ring slots per warp (DEPTH-1 rows in flight)
-constexpr int W2D_MAXK = 8;
+constexpr int W2D_MAXK = 6;  // the curve turns at 6 (fp64 star) / 4 (others); 7 and 8 only spilled at 255 registers (profiles/r01c_probe.log)
 
 __host__ __device__ constexpr int w2d_halo_left(int K) { return (K + 3) & ~3; }
 __host__ __device__ constexpr int w2d_valid(int K) { return (W2D_WIDTH - w2d_halo_left(K) - K) & ~3; }
@@ -308,7 +308,7 @@ static cudaError_t launch_warp2d_s(const T* in, T* out, const Grid& g, Domain do
     switch (K) {
 #define SB200_W2D(KK) case KK: return launch_warp2d_k<T, SHAPE, KK>(in, out, g, dom, ob, oe, tn, st)
         SB200_W2D(1); SB200_W2D(2); SB200_W2D(3); SB200_W2D(4);
-        SB200_W2D(5); SB200_W2D(6); SB200_W2D(7); SB200_W2D(8);
+        SB200_W2D(5); SB200_W2D(6);
 #undef SB200_W2D
         default: return cudaErrorInvalidValue;
     }
