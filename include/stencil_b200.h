@@ -303,8 +303,11 @@ int sb200_ipc_close(void* dev_ptr);
  * in ONE launch: the CTAs of the first and last z chunk are dispatched first and
  * push the face planes to the neighbours (peer stores + arrival signal).
  * Needs ghost == radius * max-steps-between-exchanges >= radius * steps and a
- * slab of at least 2*ghost planes; 3-D radius-1 (TMA3D family) only.
- * *arrivals = face CTAs per face of this launch (add it to wait_arrivals). */
+ * slab of at least 2*ghost planes (rows in 2-D); radius 1 only: the TMA3D family in 3-D, the
+ * WARP2D family in 2-D (faces are rows, their owners warps — the reference's RMA kernel is the
+ * 2-D case, stencil_rma.cpp:333-458).
+ * *arrivals = face owners (CTAs in 3-D, warps in 2-D) per face of this launch (add it to
+ * wait_arrivals). */
 int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
                             int hi_is_boundary, const void* a, void* b, uint32_t steps,
                             const sb200_slab_link* link, void* stream, uint32_t* arrivals);

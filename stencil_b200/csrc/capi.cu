@@ -865,8 +865,9 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     if (int rc = ensure_ready()) return rc;
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
-    if (c.kernel != SB200_KERNEL_TMA3D || desc->radius != 1)
-        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D family at radius 1");
+    const bool w2d = c.kernel == SB200_KERNEL_WARP2D;
+    if ((c.kernel != SB200_KERNEL_TMA3D && !w2d) || desc->radius != 1)
+        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D or the WARP2D family at radius 1");
     if (steps < 1 || (int)steps > c.max_k)
         return fail(SB200_ERR_INVALID, "linked sweep fuses 1..%d steps (got %u)", c.max_k, steps);
     const Grid g = make_grid(desc, ghost);
@@ -882,7 +883,7 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     L.link_lo = lo_is_boundary ? 0 : 1;
     L.link_hi = hi_is_boundary ? 0 : 1;
     L.face_planes = (int)ghost;
-    const long long plane = g.pitch_x * g.pitch_y;
+    const long long plane = w2d ? g.pitch_x : g.pitch_x * g.pitch_y;  // one index of the outermost axis
     L.peer_out_lo = link->peer_dst_lo;
     L.shift_lo = n * plane;  // my plane z is the lower neighbour's plane z + n (its upper ghosts)
     L.peer_out_hi = link->peer_dst_hi;
@@ -895,6 +896,17 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     L.err_flag = link->flags_local + 2;
     const Domain dom = make_domain(g, lo_is_boundary, hi_is_boundary);
     const long long ob = 0, oe = n;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (w2d) {
+        // face owners are warps: one per x strip and face
+        if (arrivals) *arrivals = (uint32_t)w2d_plan(g.n[0], n, (int)steps, DS().sm_count, 1, 0).nstrips;
+        const Tuning tn{DS().sm_count, tile_pref(desc)};
+        if (desc->dtype == SB200_F64)
+            CU_TRY(launch_warp2d<double>((const double*)a, (double*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+        else
+            CU_TRY(launch_warp2d<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+        return SB200_OK;
+    }
     int ntx, nty;
     if (desc->dtype == SB200_F64) {
         switch (steps) {
@@ -910,7 +922,6 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
         }
     }
     if (arrivals) *arrivals = (uint32_t)(ntx * nty);
-    cudaStream_t st = (cudaStream_t)stream;
     if (desc->dtype == SB200_F64)
         return launch_tma3d<double>((const double*)a, (double*)b, desc->dtype, g, t3_shape(desc), dom, (int)steps, ob, oe, st, L);
     return launch_tma3d<float>((const float*)a, (float*)b, desc->dtype, g, t3_shape(desc), dom, (int)steps, ob, oe, st, L);

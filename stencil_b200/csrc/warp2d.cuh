@@ -17,6 +17,7 @@
 // halo: x<0, x>=nx, rows outside [dom.lo, dom.hi)) pass through unchanged at every level.
 #pragma once
 #include "common.cuh"
+#include "slablink.cuh"
 
 namespace sb200 {
 
@@ -198,20 +199,40 @@ __device__ __forceinline__ void w2d_stream(const T* __restrict__ src, T* __restr
 }
 
 // in -> out, K fused steps, output rows [ob, oe) (slab-interior coordinates).
-template <class T, int SHAPE, int K>
+// LINKED (slablink.cuh): the launch covers a whole slab; the WARPS of its first / last row chunk
+// also own the low / high face (g rows each).  They are dispatched first (last chunk, then
+// first), acquire the neighbours' arrival counter before their first load — cp.async reads
+// through the generic proxy, so the acquire + __syncwarp is all the ordering needed — and after
+// their stream copy the face rows they stored into the ghost rows of the neighbour's destination
+// buffer with 128-bit stores over NVLink, then count themselves in with one release-add per warp.
+// The row loop carries no link code.
+template <class T, int SHAPE, int K, bool LINKED = false>
 __global__ void __launch_bounds__(32 * W2D_WARPS)
 sweep_warp2d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domain dom,
                     long long ob, long long oe, int nstrips, int chunk_rows, long long nitems,
-                    T avg) {
+                    T avg, const SlabLinkDev link) {
     constexpr int HL = w2d_halo_left(K);
     constexpr int V = w2d_valid(K);
     const int lane = threadIdx.x & 31;
     const long long item = (long long)blockIdx.x * W2D_WARPS + (threadIdx.x >> 5);
     if (item >= nitems) return;
     const int strip = (int)(item % nstrips);
-    const long long chunk = item / nstrips;
-    const long long yb = ob + chunk * chunk_rows;
-    const long long ye = (yb + chunk_rows < oe) ? yb + chunk_rows : oe;
+    long long chunk = item / nstrips;
+    if (LINKED && link.link_hi) chunk = chunk == 0 ? link.nchunks - 1 : chunk - 1;  // the last chunk first
+    const bool is_lo = LINKED && link.link_lo && chunk == 0;
+    const bool is_hi = LINKED && link.link_hi && chunk == link.nchunks - 1;
+    // linked launches balance the chunks: every chunk holds at least g rows, so the first / last
+    // chunk contains the whole low / high face
+    const long long yb = LINKED ? ob + (oe - ob) * chunk / link.nchunks : ob + chunk * chunk_rows;
+    const long long ye = LINKED ? ob + (oe - ob) * (chunk + 1) / link.nchunks
+                                : ((yb + chunk_rows < oe) ? yb + chunk_rows : oe);
+    if (LINKED && (is_lo || is_hi) && link.wait_value != 0) {
+        if (lane == 0) {
+            if (is_lo) link_wait(link.wait_lo, link.wait_value, link.err_flag);
+            if (is_hi) link_wait(link.wait_hi, link.wait_value, link.err_flag);
+        }
+        __syncwarp();
+    }
 
     const long long gx = (long long)strip * V - HL + lane * W2D_PX;  // first x of this lane
     // loads stay inside the allocation: lanes beyond it re-read the nearest valid column
@@ -247,6 +268,44 @@ sweep_warp2d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domai
     } else {
         w2d_stream<T, SHAPE, K, true>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
                                       mxmask, ring, lane_valid, ncols_valid, avg);
+    }
+    if (LINKED && (is_lo || is_hi)) {
+        // face push: every lane copies the face-row points IT stored (its own writes: no barrier
+        // before the read-back) into the neighbour's ghost rows
+        T* home = out + g.idx(gx, 0, 0);
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) {
+            if (side == 0 ? !is_lo : !is_hi) continue;
+            const long long y0 = side == 0 ? 0 : g.n[1] - link.face_planes;
+            const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
+                                     (side == 0 ? link.shift_lo : link.shift_hi);
+            if (lane_valid) {
+#pragma unroll 1
+                for (int p = 0; p < link.face_planes; ++p) {
+                    T* srow = home + (y0 + p) * g.pitch_x;
+                    if (ncols_valid >= W2D_PX) {
+                        Row4<T> r;
+                        if constexpr (sizeof(T) == 4) {
+                            const float4 f = *reinterpret_cast<const float4*>(srow);
+                            r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w;
+                        } else {
+                            const double2 a = reinterpret_cast<const double2*>(srow)[0];
+                            const double2 b = reinterpret_cast<const double2*>(srow)[1];
+                            r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y;
+                        }
+                        w2d_store(srow + rdelta, r);
+                    } else {
+                        for (int i = 0; i < ncols_valid; ++i) srow[rdelta + i] = srow[i];
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_system();
+            if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
+            if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
+        }
     }
 }
 
@@ -292,21 +351,34 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
 
 template <class T, int SHAPE, int K>
 static cudaError_t launch_warp2d_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
-                                   long long oe, const Tuning& tn, cudaStream_t st) {
+                                   long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link_in) {
     if (oe <= ob) return cudaSuccess;
     const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, 1, tn.prefer_chunk);
     const T avg = Avg<T>::value(SHAPE, 2, 1);
+    if (link_in && (link_in->link_lo || link_in->link_hi)) {
+        SlabLinkDev link = *link_in;
+        long long nc = p.nchunks;
+        if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
+        if (nc < 1) nc = 1;
+        link.nchunks = (int)nc;
+        const long long nitems = nc * p.nstrips;
+        const unsigned blocks = (unsigned)((nitems + W2D_WARPS - 1) / W2D_WARPS);
+        sweep_warp2d_kernel<T, SHAPE, K, true><<<blocks, 32 * W2D_WARPS, 0, st>>>(
+            in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, nitems, avg, link);
+        return cudaGetLastError();
+    }
     const unsigned blocks = (unsigned)((p.nitems + W2D_WARPS - 1) / W2D_WARPS);
-    sweep_warp2d_kernel<T, SHAPE, K><<<blocks, 32 * W2D_WARPS, 0, st>>>(
-        in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, p.nitems, avg);
+    sweep_warp2d_kernel<T, SHAPE, K, false><<<blocks, 32 * W2D_WARPS, 0, st>>>(
+        in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, p.nitems, avg, SlabLinkDev{});
     return cudaGetLastError();
 }
 
 template <class T, int SHAPE>
 static cudaError_t launch_warp2d_s(const T* in, T* out, const Grid& g, Domain dom, int K,
-                                   long long ob, long long oe, const Tuning& tn, cudaStream_t st) {
+                                   long long ob, long long oe, const Tuning& tn, cudaStream_t st,
+                                   const SlabLinkDev* link) {
     switch (K) {
-#define SB200_W2D(KK) case KK: return launch_warp2d_k<T, SHAPE, KK>(in, out, g, dom, ob, oe, tn, st)
+#define SB200_W2D(KK) case KK: return launch_warp2d_k<T, SHAPE, KK>(in, out, g, dom, ob, oe, tn, st, link)
         SB200_W2D(1); SB200_W2D(2); SB200_W2D(3); SB200_W2D(4);
         SB200_W2D(5); SB200_W2D(6);
 #undef SB200_W2D
@@ -316,9 +388,10 @@ static cudaError_t launch_warp2d_s(const T* in, T* out, const Grid& g, Domain do
 
 template <class T>
 static cudaError_t launch_warp2d(const T* in, T* out, const Grid& g, int shape, Domain dom, int K,
-                                 long long ob, long long oe, const Tuning& tn, cudaStream_t st) {
-    return shape == STAR ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, tn, st)
-                         : launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, tn, st);
+                                 long long ob, long long oe, const Tuning& tn, cudaStream_t st,
+                                 const SlabLinkDev* link = nullptr) {
+    return shape == STAR ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, tn, st, link)
+                         : launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, tn, st, link);
 }
 
 }  // namespace sb200

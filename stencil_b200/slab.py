@@ -5,12 +5,12 @@ The reference decomposes its grid over an 8x8 core mesh and exchanges halos ever
 rank g owns a contiguous slab of planes plus `ghost = radius * k` ghost planes per
 internal face, exchanged once per fused block of k time steps:
 
-  exchange="p2p" (default for the 3-D radius-1 family): ONE launch per block; its face
-    CTAs run first and store their planes straight into the neighbours' ghost planes over
+  exchange="p2p" (default for the radius-1 families, TMA3D in 3-D and WARP2D in 2-D): ONE launch
+    per block; its face CTAs (warps in 2-D) run first and store their planes straight into the neighbours' ghost planes over
     NVLink (CUDA IPC peer mappings), signalling arrival counters the neighbours' next launch
     acquires — no NCCL call, no extra launch, no host sync on the data path
     (csrc/tma3d.cuh: SlabLinkDev).
-  exchange="nccl" (2-D grids, generic kernel, and the measured baseline):
+  exchange="nccl" (radius > 1, generic kernel, and the measured baseline):
     faces first (side stream)  ->  send/recv face planes (NCCL, NVLink)   \
     interior planes (main stream, concurrently)                             -> join
 
@@ -240,11 +240,11 @@ class SlabSweep:
                              f"({self.ghost} each); use fewer ranks or a smaller time block")
         auto = exchange == "auto"
         if auto:
-            exchange = "p2p" if (world > 1 and self.kernel == capi.KERNEL_TMA3D and self.r == 1) else "nccl"
+            exchange = "p2p" if (world > 1 and self._linkable()) else "nccl"
         if exchange not in ("p2p", "nccl"):
             raise ValueError(f"exchange must be 'auto', 'p2p' or 'nccl' (got {exchange!r})")
-        if exchange == "p2p" and (self.kernel != capi.KERNEL_TMA3D or self.r != 1):
-            raise ValueError("exchange='p2p' needs the 3-D radius-1 kernel family")
+        if exchange == "p2p" and not self._linkable():
+            raise ValueError("exchange='p2p' needs a radius-1 kernel family (TMA3D in 3-D, WARP2D in 2-D)")
         self.exchange = exchange if world > 1 else "none"
         p2p = self.exchange == "p2p"
         factory = engine_factory or (lambda d, g: CudaEngine(d, g, _current_device(), exportable=p2p))
@@ -276,6 +276,10 @@ class SlabSweep:
                     self.exchange = "nccl"
                     self.kernels_per_launch_unit = 1 + (not self.lo_b) + (not self.hi_b)
                     self.eng = (engine_factory or (lambda d, g: CudaEngine(d, g, _current_device())))(desc, self.ghost)
+
+    def _linkable(self) -> bool:
+        """Kernel families with the fused peer-store exchange (sb200_sweep_slab_linked)."""
+        return self.r == 1 and self.kernel in (capi.KERNEL_TMA3D, capi.KERNEL_WARP2D)
 
     def _all_ok(self, ok: bool) -> bool:
         """Logical AND of `ok` over all ranks (engines that are not CUDA-backed skip it)."""

@@ -160,7 +160,8 @@ def test_slab_exchange_matches_single_grid(tmp_path, world, n, shape, dtype, T, 
     assert np.array_equal(got.view(np.uint8), want[1:-1].view(np.uint8))
 
 
-@pytest.mark.parametrize("world,n,T,k", [(2, (20, 12, 16), 5, 2), (3, (10, 9, 18), 7, 3)])
+@pytest.mark.parametrize("world,n,T,k", [(2, (20, 12, 16), 5, 2), (3, (10, 9, 18), 7, 3),
+                                         (2, (24, 40), 9, 4)])    # 2-D: the linked flow over row faces
 def test_slab_linked_flow_matches_single_grid(tmp_path, world, n, T, k):
     """exchange="p2p": one linked launch per fused block, remainder block included."""
     out = str(tmp_path / "res.npy")
@@ -173,10 +174,15 @@ def test_slab_linked_flow_matches_single_grid(tmp_path, world, n, T, k):
 
 def test_exchange_mode_selection():
     d3 = capi.make_desc((8, 8, 8), time_block=2)
-    d2 = capi.make_desc((8, 8), shape=capi.BOX)
+    d2 = capi.make_desc((8, 16), shape=capi.BOX)
+    d2r = capi.make_desc((8, 16), radius=2)
     assert slab.SlabSweep(d3, 0, 1, engine_factory=OracleEngine).exchange == "none"
+    # the fused exchange exists for the radius-1 families (TMA3D planes, WARP2D rows) only
+    assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p").exchange == "p2p"
+    assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"
+    assert slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"
     with pytest.raises(ValueError):
-        slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
+        slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
     with pytest.raises(ValueError):
         slab.SlabSweep(d3, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="bogus")
 

@@ -20,6 +20,8 @@ for n_local, shape, dtype, T, k, exch in [((256, 200, 64), capi.STAR, capi.F64, 
                                            ((256, 200, 64), capi.STAR, capi.F32, 6, 3, "p2p"),
                                            ((130, 61, 12), capi.STAR, capi.F64, 31, 2, "p2p"),
                                            ((1000, 256), capi.BOX, capi.F32, 19, 4, "nccl"),
+                                           ((1000, 256), capi.BOX, capi.F32, 19, 4, "p2p"),    # 2-D fused exchange: faces are rows
+                                           ((4096, 512), capi.STAR, capi.F64, 26, 6, "p2p"),
                                            ((300, 128, 40), capi.BOX, capi.F64, 3, 1, "nccl"),
                                            ((300, 128, 40), capi.BOX, capi.F64, 9, 2, "p2p")]:
     d = capi.make_desc(n_local, 1, shape, dtype, T, time_block=k)
