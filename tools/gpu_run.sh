@@ -44,7 +44,9 @@ task() {
       for c in ${CHUNKS:-auto 7 9 11 13}; do if [ $c = auto ]; then timeout 120 python tools/e2e_probe.py 2>&1 | tail -1; else SB200_PIPELINE_CHUNKS=$c timeout 120 python tools/e2e_probe.py 2>&1 | tail -1; fi; done | tee gpurun_out/e2e_probe.log ;;
     multi) local n=${1:-2}; timeout 300 python -m pytest tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -3
       timeout 300 $TR --nproc-per-node $n --master-port 29611 tools/multi_check.py 2>&1 | tail -8 | tee gpurun_out/multi_check_n$n.log
-      timeout 300 $TR --nproc-per-node $n --master-port 29612 tools/config5.py --mode strong --steps 40 2>&1 | grep '^{' | tee gpurun_out/config5_n$n.log ;;
+      timeout 300 $TR --nproc-per-node $n --master-port 29612 tools/config5.py --mode strong --steps 40 2>&1 | grep '^{' | tee gpurun_out/config5_n$n.log
+      for ex in p2p nccl; do timeout 300 $TR --nproc-per-node $n --master-port 29613 tools/config4.py --exchange $ex 2>&1 | grep '^{'; done | tee gpurun_out/config4_n$n.log
+      timeout 300 python tools/config4.py 2>&1 | grep '^{' | tee -a gpurun_out/config4_n$n.log ;;
     n8) nvidia-smi topo -m > gpurun_out/topo_n8.txt 2>&1; lscpu | grep -E "NUMA|Socket|Model name|^CPU\(s\)" > gpurun_out/lscpu_n8.txt 2>&1
       timeout 300 tools/pcie_probe 512 > gpurun_out/pcie_probe_n8.log 2>&1; echo "probe rc=$?"
       task torchbench 8 n8
