@@ -1185,6 +1185,18 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     for (const auto& o : ops)
         for (int w : o.wait)
             if (w >= 0 && !op_done[(size_t)w]) op_done[(size_t)w] = events.make();
+    // SB200_PIPELINE_TRACE=<file>: a start and an end event around every op, written out as CSV
+    // after the call (diagnostics of the schedule; the extra events cost a few microseconds)
+    const char* trace_path = getenv("SB200_PIPELINE_TRACE");
+    std::vector<cudaEvent_t> t_begin, t_end;
+    if (trace_path) {
+        t_begin.resize(ops.size());
+        t_end.resize(ops.size());
+        for (size_t j = 0; j < ops.size(); ++j) {
+            t_begin[j] = events.make(cudaEventDefault);
+            t_end[j] = events.make(cudaEventDefault);
+        }
+    }
     CU_TRY(events.err);
     CU_TRY(cudaEventRecord(ev[0], st));
     CU_TRY(cudaStreamWaitEvent(D.st_in, ev[0], 0));
@@ -1205,8 +1217,10 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     for (size_t j = 0; j < ops.size(); ++j) {
         const sb200_pipe_op& o = ops[j];
         if (o.kind != SB200_PIPE_UPLOAD) continue;
+        if (trace_path) CU_TRY(cudaEventRecord(t_begin[j], D.st_in));
         CU_TRY(cudaMemcpyAsync((char*)D.staging + o.lo * outer_bytes, (const char*)in + o.lo * outer_bytes,
                                (size_t)(o.hi - o.lo) * outer_bytes, cudaMemcpyHostToDevice, D.st_in));
+        if (trace_path) CU_TRY(cudaEventRecord(t_end[j], D.st_in));
         if (op_done[j]) CU_TRY(cudaEventRecord(op_done[j], D.st_in));
         if (--uploads_left == 0) CU_TRY(cudaEventRecord(ev[1], D.st_in));
         if (sync && ++uploads_issued == sync->zone_uploads) CU_TRY(cudaEventRecord(sync->zones_read, D.st_in));
@@ -1223,6 +1237,7 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
         cudaStream_t ss = stream_of(o);
         for (int w : o.wait)
             if (w >= 0) CU_TRY(cudaStreamWaitEvent(ss, op_done[(size_t)w], 0));
+        if (trace_path) CU_TRY(cudaEventRecord(t_begin[j], ss));
         switch (o.kind) {
             case SB200_PIPE_UNPACK: {
                 const long long rb = o.lo * rows_per_outer, re = o.hi * rows_per_outer;
@@ -1246,6 +1261,7 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
                 if (int rc = download_interior_range(desc, buf[o.src], host_dst, o.lo, o.hi, ss)) return rc;
                 break;
         }
+        if (trace_path) CU_TRY(cudaEventRecord(t_end[j], ss));
         if (op_done[j]) CU_TRY(cudaEventRecord(op_done[j], ss));
     }
     if (!first_download) CU_TRY(cudaEventRecord(ev[2], D.st_out));
@@ -1256,6 +1272,19 @@ static int run_host_pipelined(const sb200_desc* desc, const Choice& c, void* in,
     CU_TRY(cudaStreamSynchronize(st));
     CU_TRY(cudaStreamSynchronize(D.st_in));
     const auto w1 = std::chrono::steady_clock::now();
+    if (trace_path) {
+        if (FILE* f = fopen(trace_path, "w")) {
+            fprintf(f, "op,kind,stream,parallelogram,block,steps,lo,hi,begin_ms,end_ms,device\n");
+            for (size_t j = 0; j < ops.size(); ++j) {
+                float b = 0, e = 0;
+                cudaEventElapsedTime(&b, ev[0], t_begin[j]);
+                cudaEventElapsedTime(&e, ev[0], t_end[j]);
+                fprintf(f, "%zu,%d,%d,%d,%d,%u,%lld,%lld,%.4f,%.4f,%d\n", j, ops[j].kind, ops[j].stream, ops[j].parallelogram,
+                        ops[j].block, ops[j].steps, (long long)ops[j].lo, (long long)ops[j].hi, b, e, D.device);
+            }
+            fclose(f);
+        }
+    }
     if (timing) {
         float ms = 0;
         cudaEventElapsedTime(&ms, ev[0], ev[1]); timing->h2d_ms = ms;    // all upload chunks
