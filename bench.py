@@ -194,8 +194,8 @@ def run_reference(args):
 C5_NZ, C5_NXY, C5_T = 2048, 1024, 40
 # The 1-GPU run of this very leg (same seed, same T): the checksum every N must reproduce bit
 # for bit, and the base of the strong-scaling efficiency together with the SM clock it ran at.
-C5_BASE = {"checksum": "0xcc6b79639046d6e0", "value": 588.9, "sm_mhz": 1687.0,
-           "source": "profiles/r02b_bench_n1.json (bench.py --steps 5, 1 x B200, sw_power_cap)"}
+C5_BASE = {"checksum": "0xcc6b79639046d6e0", "value": 661.2, "sm_mhz": 1770.0,
+           "source": "profiles/r02g_bench_n1.json (bench.py --steps 10, 1 x B200, sw_power_cap)"}
 
 
 def _allreduce_u64_sum(torch, dist, world, c: int) -> int:
