@@ -12,7 +12,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 raw, source = sys.argv[1], sys.argv[2]
 rows = list(csv.reader(open(raw)))
 hdr, units = rows[0], rows[1]
-r = [x for x in rows[2:] if "sweep_tma3d_kernel<double, (int)2, (int)0, (bool)0>" in x[hdr.index("Kernel Name")]][-1]
+name = hdr.index("Kernel Name")   # ncu prints template arguments as "<double, 2, 0, 0>" or "<double, (int)2, ...>"
+r = [x for x in rows[2:] if x[name].replace("(int)", "").replace("(bool)", "").startswith("void sweep_tma3d_kernel<double, 2, 0, 0>")][-1]
 
 
 def val(name):
