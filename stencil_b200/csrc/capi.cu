@@ -866,8 +866,8 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
     const bool w2d = c.kernel == SB200_KERNEL_WARP2D;
-    if ((c.kernel != SB200_KERNEL_TMA3D && !w2d) || desc->radius != 1)
-        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the TMA3D or the WARP2D family at radius 1");
+    if (!w2d && (c.kernel != SB200_KERNEL_TMA3D || desc->radius != 1))
+        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the WARP2D family or the TMA3D family at radius 1");
     if (steps < 1 || (int)steps > c.max_k)
         return fail(SB200_ERR_INVALID, "linked sweep fuses 1..%d steps (got %u)", c.max_k, steps);
     const Grid g = make_grid(desc, ghost);
@@ -899,12 +899,18 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     cudaStream_t st = (cudaStream_t)stream;
     if (w2d) {
         // face owners are warps: one per x strip and face
-        if (arrivals) *arrivals = (uint32_t)w2d_plan(g.n[0], n, (int)steps, DS().sm_count, 1, 0).nstrips;
+        if (arrivals) *arrivals = (uint32_t)w2d_plan(g.n[0], n, (int)steps, DS().sm_count, g.r, 0).nstrips;
         const Tuning tn{DS().sm_count, tile_pref(desc)};
-        if (desc->dtype == SB200_F64)
+        if (g.r > 1) {
+            if (desc->dtype == SB200_F64)
+                CU_TRY(launch_warp2dr<double>((const double*)a, (double*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+            else
+                CU_TRY(launch_warp2dr<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+        } else if (desc->dtype == SB200_F64) {
             CU_TRY(launch_warp2d<double>((const double*)a, (double*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
-        else
+        } else {
             CU_TRY(launch_warp2d<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+        }
         return SB200_OK;
     }
     int ntx, nty;

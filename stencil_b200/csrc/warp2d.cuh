@@ -198,6 +198,54 @@ __device__ __forceinline__ void w2d_stream(const T* __restrict__ src, T* __restr
     }
 }
 
+// ---- slab link at warp granularity (shared with warp2dr.cuh) ------------------------------------
+// A face-owning warp waits until the neighbour's previous launch has delivered the ghost rows it
+// is about to read: lane 0 acquires the arrival counter, __syncwarp orders the other lanes'
+// loads behind it (cp.async reads through the generic proxy: no proxy fence is needed).
+__device__ __forceinline__ void w2d_link_acquire(const SlabLinkDev& link, bool is_lo, bool is_hi, int lane) {
+    if ((is_lo || is_hi) && link.wait_value != 0) {
+        if (lane == 0) {
+            if (is_lo) link_wait(link.wait_lo, link.wait_value, link.err_flag);
+            if (is_hi) link_wait(link.wait_hi, link.wait_value, link.err_flag);
+        }
+        __syncwarp();
+    }
+}
+// After its stream a face-owning warp copies the face-row points its lanes stored (own writes:
+// no barrier before the read-back) into the ghost rows of the neighbour's destination buffer
+// with 128-bit stores over NVLink and counts itself in with one release-add.
+template <class T>
+__device__ __forceinline__ void w2d_link_push(T* __restrict__ out, const Grid& g, long long gx, bool lane_valid,
+                                              int ncols_valid, const SlabLinkDev& link, bool is_lo, bool is_hi,
+                                              int lane) {
+    if (!(is_lo || is_hi)) return;
+    T* home = out + g.idx(gx, 0, 0);
+#pragma unroll 1
+    for (int side = 0; side < 2; ++side) {
+        if (side == 0 ? !is_lo : !is_hi) continue;
+        const long long y0 = side == 0 ? 0 : g.n[1] - link.face_planes;
+        const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
+                                 (side == 0 ? link.shift_lo : link.shift_hi);
+        if (lane_valid) {
+#pragma unroll 1
+            for (int p = 0; p < link.face_planes; ++p) {
+                T* srow = home + (y0 + p) * g.pitch_x;
+                if (ncols_valid >= W2D_PX) {
+                    w2d_store(srow + rdelta, w2d_read_row(srow));
+                } else {
+                    for (int i = 0; i < ncols_valid; ++i) srow[rdelta + i] = srow[i];
+                }
+            }
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence_system();
+        if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
+        if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
+    }
+}
+
 // in -> out, K fused steps, output rows [ob, oe) (slab-interior coordinates).
 // LINKED (slablink.cuh): the launch covers a whole slab; the WARPS of its first / last row chunk
 // also own the low / high face (g rows each).  They are dispatched first (last chunk, then
@@ -226,13 +274,7 @@ sweep_warp2d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domai
     const long long yb = LINKED ? ob + (oe - ob) * chunk / link.nchunks : ob + chunk * chunk_rows;
     const long long ye = LINKED ? ob + (oe - ob) * (chunk + 1) / link.nchunks
                                 : ((yb + chunk_rows < oe) ? yb + chunk_rows : oe);
-    if (LINKED && (is_lo || is_hi) && link.wait_value != 0) {
-        if (lane == 0) {
-            if (is_lo) link_wait(link.wait_lo, link.wait_value, link.err_flag);
-            if (is_hi) link_wait(link.wait_hi, link.wait_value, link.err_flag);
-        }
-        __syncwarp();
-    }
+    if (LINKED) w2d_link_acquire(link, is_lo, is_hi, lane);
 
     const long long gx = (long long)strip * V - HL + lane * W2D_PX;  // first x of this lane
     // loads stay inside the allocation: lanes beyond it re-read the nearest valid column
@@ -269,44 +311,7 @@ sweep_warp2d_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domai
         w2d_stream<T, SHAPE, K, true>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
                                       mxmask, ring, lane_valid, ncols_valid, avg);
     }
-    if (LINKED && (is_lo || is_hi)) {
-        // face push: every lane copies the face-row points IT stored (its own writes: no barrier
-        // before the read-back) into the neighbour's ghost rows
-        T* home = out + g.idx(gx, 0, 0);
-#pragma unroll 1
-        for (int side = 0; side < 2; ++side) {
-            if (side == 0 ? !is_lo : !is_hi) continue;
-            const long long y0 = side == 0 ? 0 : g.n[1] - link.face_planes;
-            const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
-                                     (side == 0 ? link.shift_lo : link.shift_hi);
-            if (lane_valid) {
-#pragma unroll 1
-                for (int p = 0; p < link.face_planes; ++p) {
-                    T* srow = home + (y0 + p) * g.pitch_x;
-                    if (ncols_valid >= W2D_PX) {
-                        Row4<T> r;
-                        if constexpr (sizeof(T) == 4) {
-                            const float4 f = *reinterpret_cast<const float4*>(srow);
-                            r.v[0] = f.x; r.v[1] = f.y; r.v[2] = f.z; r.v[3] = f.w;
-                        } else {
-                            const double2 a = reinterpret_cast<const double2*>(srow)[0];
-                            const double2 b = reinterpret_cast<const double2*>(srow)[1];
-                            r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y;
-                        }
-                        w2d_store(srow + rdelta, r);
-                    } else {
-                        for (int i = 0; i < ncols_valid; ++i) srow[rdelta + i] = srow[i];
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) {
-            __threadfence_system();
-            if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
-            if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
-        }
-    }
+    if (LINKED) w2d_link_push<T>(out, g, gx, lane_valid, ncols_valid, link, is_lo, is_hi, lane);
 }
 
 struct W2dPlan {

@@ -188,11 +188,11 @@ __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restr
 
 // in -> out, K fused steps of the radius-R star, output rows [ob, oe) (slab-interior
 // coordinates).  Work item = (x strip, y chunk), one per warp, as in sweep_warp2d_kernel.
-template <class T, int R, int K, int SHAPE = STAR>
+template <class T, int R, int K, int SHAPE = STAR, bool LINKED = false>
 __global__ void __launch_bounds__(32 * W2D_WARPS)
 sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Domain dom,
                      long long ob, long long oe, int nstrips, int chunk_rows, long long nitems,
-                     T avg) {
+                     T avg, const SlabLinkDev link) {
     constexpr int HL = w2r_halo_left(K, R);
     constexpr int V = w2r_valid(K, R);
     constexpr int D = w2r_depth(R);
@@ -200,9 +200,16 @@ sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Doma
     const long long item = (long long)blockIdx.x * W2D_WARPS + (threadIdx.x >> 5);
     if (item >= nitems) return;
     const int strip = (int)(item % nstrips);
-    const long long chunk = item / nstrips;
-    const long long yb = ob + chunk * chunk_rows;
-    const long long ye = (yb + chunk_rows < oe) ? yb + chunk_rows : oe;
+    long long chunk = item / nstrips;
+    // LINKED: as in sweep_warp2d_kernel (faces are g = R * k rows, their owners the warps of the
+    // first / last row chunk, dispatched first)
+    if (LINKED && link.link_hi) chunk = chunk == 0 ? link.nchunks - 1 : chunk - 1;
+    const bool is_lo = LINKED && link.link_lo && chunk == 0;
+    const bool is_hi = LINKED && link.link_hi && chunk == link.nchunks - 1;
+    const long long yb = LINKED ? ob + (oe - ob) * chunk / link.nchunks : ob + chunk * chunk_rows;
+    const long long ye = LINKED ? ob + (oe - ob) * (chunk + 1) / link.nchunks
+                                : ((yb + chunk_rows < oe) ? yb + chunk_rows : oe);
+    if (LINKED) w2d_link_acquire(link, is_lo, is_hi, lane);
 
     const long long gx = (long long)strip * V - HL + lane * W2D_PX;
     long long gx_ld = gx < -(long long)g.ox ? -(long long)g.ox : gx;
@@ -240,17 +247,29 @@ sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Doma
         w2r_stream<T, R, K, true, SHAPE>(src, dst, g.pitch_x, nsteps, j_dom_lo, j_dom_hi, j_row_lo, j_row_hi,
                                   mxmask, ring, lane_valid, ncols_valid, avg);
     }
+    if (LINKED) w2d_link_push<T>(out, g, gx, lane_valid, ncols_valid, link, is_lo, is_hi, lane);
 }
 
 template <class T, int R, int K, int SHAPE = STAR>
 static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
-                                    long long oe, const Tuning& tn, cudaStream_t st) {
+                                    long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link_in) {
     if (oe <= ob) return cudaSuccess;
     const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, R, tn.prefer_chunk);
     const T avg = Avg<T>::value(SHAPE, 2, R);
+    if (link_in && (link_in->link_lo || link_in->link_hi)) {
+        SlabLinkDev link = *link_in;
+        long long nc = p.nchunks;
+        if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
+        if (nc < 1) nc = 1;
+        link.nchunks = (int)nc;
+        const long long nitems = nc * p.nstrips;
+        sweep_warp2dr_kernel<T, R, K, SHAPE, true><<<(unsigned)((nitems + W2D_WARPS - 1) / W2D_WARPS), 32 * W2D_WARPS, 0, st>>>(
+            in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, nitems, avg, link);
+        return cudaGetLastError();
+    }
     const unsigned blocks = (unsigned)((p.nitems + W2D_WARPS - 1) / W2D_WARPS);
-    sweep_warp2dr_kernel<T, R, K, SHAPE><<<blocks, 32 * W2D_WARPS, 0, st>>>(
-        in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, p.nitems, avg);
+    sweep_warp2dr_kernel<T, R, K, SHAPE, false><<<blocks, 32 * W2D_WARPS, 0, st>>>(
+        in, out, g, dom, ob, oe, p.nstrips, p.chunk_rows, p.nitems, avg, SlabLinkDev{});
     return cudaGetLastError();
 }
 
@@ -258,18 +277,18 @@ static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain d
 // (25-point), K fused steps (1 .. w2r_box_max_k).
 template <class T>
 static cudaError_t launch_warp2dr(const T* in, T* out, const Grid& g, int shape, Domain dom, int K, long long ob,
-                                  long long oe, const Tuning& tn, cudaStream_t st) {
+                                  long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link = nullptr) {
     if (shape == BOX) {
         if (g.r != 2 || K < 1 || K > w2r_box_max_k(2, (int)sizeof(T))) return cudaErrorInvalidValue;
-        if (K == 1) return launch_warp2dr_k<T, 2, 1, BOX>(in, out, g, dom, ob, oe, tn, st);
+        if (K == 1) return launch_warp2dr_k<T, 2, 1, BOX>(in, out, g, dom, ob, oe, tn, st, link);
         if constexpr (w2r_box_max_k(2, (int)sizeof(T)) >= 2)
-            return launch_warp2dr_k<T, 2, 2, BOX>(in, out, g, dom, ob, oe, tn, st);
+            return launch_warp2dr_k<T, 2, 2, BOX>(in, out, g, dom, ob, oe, tn, st, link);
         return cudaErrorInvalidValue;
     }
     if (K < 1 || g.r < 2 || g.r > 4 || K > w2r_max_k(g.r, (int)sizeof(T))) return cudaErrorInvalidValue;
 #define SB200_W2R(RR, KK) \
     if constexpr (KK <= w2r_max_k(RR, (int)sizeof(T))) \
-        if (g.r == RR && K == KK) return launch_warp2dr_k<T, RR, KK>(in, out, g, dom, ob, oe, tn, st)
+        if (g.r == RR && K == KK) return launch_warp2dr_k<T, RR, KK>(in, out, g, dom, ob, oe, tn, st, link)
     SB200_W2R(2, 1); SB200_W2R(2, 2); SB200_W2R(2, 3); SB200_W2R(2, 4);
     SB200_W2R(3, 1); SB200_W2R(3, 2);
     SB200_W2R(4, 1); SB200_W2R(4, 2);

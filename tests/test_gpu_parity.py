@@ -303,34 +303,38 @@ def test_resident2d_auto_and_limits(gpu):
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("shape", [capi.STAR, capi.BOX])
-@pytest.mark.parametrize("n,T,k", [
-    ((70, 66, 12), 4, 2), ((130, 61, 9), 5, 2), ((64, 64, 40), 3, 1),            # 3-D: TMA3D, faces are planes
-    ((300, 40), 9, 4), ((131, 24), 7, 2), ((700, 300), 13, 6), ((64, 17), 5, 1),  # 2-D: WARP2D, faces are rows
+@pytest.mark.parametrize("n,r,T,k", [
+    ((70, 66, 12), 1, 4, 2), ((130, 61, 9), 1, 5, 2), ((64, 64, 40), 1, 3, 1),            # 3-D: TMA3D, faces are planes
+    ((300, 40), 1, 9, 4), ((131, 24), 1, 7, 2), ((700, 300), 1, 13, 6), ((64, 17), 1, 5, 1),  # 2-D: WARP2D, faces are rows
+    ((300, 64), 2, 7, 2), ((131, 40), 2, 5, 1), ((260, 90), 3, 5, 2), ((200, 70), 4, 3, 1),   # 2-D radius > 1 (warp2dr)
 ])
-def test_slab_link_self_periodic(gpu, n, T, k, shape, dtype):
+def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     """The fused halo exchange (sb200_sweep_slab_linked: peer stores + arrival counters) on
     ONE GPU: the slab is its own lower and upper neighbour, i.e. periodic along the outermost
     axis.  For T <= n_outer that equals the middle copy of three stacked copies swept with the
     ordinary Dirichlet oracle, bit for bit."""
     import torch
+    if shape == capi.BOX and r > 2:
+        pytest.skip("no fused 2-D box kernel beyond radius 2")
+    d = capi.make_desc(n, r, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
+    k = min(k, int(capi.lib().sb200_max_time_block(ctypes.byref(d))))
     no = n[-1]
-    g = k  # ghost planes / rows = radius * fused depth
-    assert T <= no
+    g = r * k  # ghost planes / rows = radius * fused depth
+    assert T * r <= no
     code = oracle.F64 if dtype == np.float64 else oracle.F32
-    P = oracle.fill(n, 1, code, oracle.INIT_RANDOM, 11)
+    P = oracle.fill(n, r, code, oracle.INIT_RANDOM, 11)
     n3 = tuple(n[:-1]) + (3 * no,)
-    A3, B3 = oracle.fill(n3, 1, code, oracle.INIT_REF), oracle.fill(n3, 1, code, oracle.INIT_REF)
+    A3, B3 = oracle.fill(n3, r, code, oracle.INIT_REF), oracle.fill(n3, r, code, oracle.INIT_REF)
     for c in range(3):
-        A3[1 + c * no:1 + (c + 1) * no] = P[1:-1]
-    want3 = B3 if oracle.sweep(n3, 1, shape, T, A3, B3, threads=oracle.max_threads()) else A3
-    inner = (slice(None),) + (slice(1, -1),) * (len(n) - 1)
-    want = want3[1 + no:1 + 2 * no][inner]
+        A3[r + c * no:r + (c + 1) * no] = P[r:-r]
+    want3 = B3 if oracle.sweep(n3, r, shape, T, A3, B3, threads=oracle.max_threads()) else A3
+    inner = (slice(None),) + (slice(r, -r),) * (len(n) - 1)
+    want = want3[r + no:r + 2 * no][inner]
 
-    d = capi.make_desc(n, 1, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
     dg = sweep.DeviceGrids(d, ghost=g)
-    S = np.empty((no + 2 * (1 + g),) + P.shape[1:], dtype)
+    S = np.empty((no + 2 * (r + g),) + P.shape[1:], dtype)
     for p in range(S.shape[0]):
-        S[p] = P[1 + (p - (1 + g)) % no]
+        S[p] = P[r + (p - (r + g)) % no]
     dg.upload(S, 0)
     dg.upload(S, 1)
     flags = torch.zeros(capi.LINK_FLAG_WORDS, dtype=torch.int32, device="cuda")
@@ -354,7 +358,7 @@ def test_slab_link_self_periodic(gpu, n, T, k, shape, dtype):
     capi.check(L.sb200_link_status(flags.data_ptr(), words))
     assert words[2] == 0, "a face owner timed out waiting for its neighbour"
     assert words[0] == arrivals and words[1] == arrivals
-    got = dg.download(cur)[1 + g:1 + g + no][inner]
+    got = dg.download(cur)[r + g:r + g + no][inner]
     assert np.array_equal(got.view(np.uint8), np.ascontiguousarray(want).view(np.uint8))
 
 

@@ -175,14 +175,19 @@ def test_slab_linked_flow_matches_single_grid(tmp_path, world, n, T, k):
 def test_exchange_mode_selection():
     d3 = capi.make_desc((8, 8, 8), time_block=2)
     d2 = capi.make_desc((8, 16), shape=capi.BOX)
-    d2r = capi.make_desc((8, 16), radius=2)
+    d2r = capi.make_desc((8, 32), radius=2)
+    d3r = capi.make_desc((8, 8, 16), radius=2)
+    d2g = capi.make_desc((8, 32), radius=3, shape=capi.BOX)
     assert slab.SlabSweep(d3, 0, 1, engine_factory=OracleEngine).exchange == "none"
-    # the fused exchange exists for the radius-1 families (TMA3D planes, WARP2D rows) only
+    # the fused exchange exists for the WARP2D family (rows) and for TMA3D at radius 1 (planes)
     assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p").exchange == "p2p"
     assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"
-    assert slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"
-    with pytest.raises(ValueError):
-        slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
+    assert slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"
+    assert slab.SlabSweep(d3r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"   # 13-point: tma3dr
+    assert slab.SlabSweep(d2g, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"   # generic kernel
+    for d in (d3r, d2g):
+        with pytest.raises(ValueError):
+            slab.SlabSweep(d, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
     with pytest.raises(ValueError):
         slab.SlabSweep(d3, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="bogus")
 

@@ -15,16 +15,24 @@ torch.cuda.set_device(local)
 capi.check(capi.lib().sb200_init(local))
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for n_local, shape, dtype, T, k, exch in [((256, 200, 64), capi.STAR, capi.F64, 7, 2, "p2p"),
-                                           ((256, 200, 64), capi.STAR, capi.F64, 7, 2, "nccl"),
-                                           ((256, 200, 64), capi.STAR, capi.F32, 6, 3, "p2p"),
-                                           ((130, 61, 12), capi.STAR, capi.F64, 31, 2, "p2p"),
-                                           ((1000, 256), capi.BOX, capi.F32, 19, 4, "nccl"),
-                                           ((1000, 256), capi.BOX, capi.F32, 19, 4, "p2p"),    # 2-D fused exchange: faces are rows
-                                           ((4096, 512), capi.STAR, capi.F64, 26, 6, "p2p"),
-                                           ((300, 128, 40), capi.BOX, capi.F64, 3, 1, "nccl"),
-                                           ((300, 128, 40), capi.BOX, capi.F64, 9, 2, "p2p")]:
-    d = capi.make_desc(n_local, 1, shape, dtype, T, time_block=k)
+CASES = [  # n_local, radius, shape, dtype, T, k, exchange
+    ((256, 200, 64), 1, capi.STAR, capi.F64, 7, 2, "p2p"),
+    ((256, 200, 64), 1, capi.STAR, capi.F64, 7, 2, "nccl"),
+    ((256, 200, 64), 1, capi.STAR, capi.F32, 6, 3, "p2p"),
+    ((130, 61, 12), 1, capi.STAR, capi.F64, 31, 2, "p2p"),
+    ((1000, 256), 1, capi.BOX, capi.F32, 19, 4, "nccl"),
+    ((1000, 256), 1, capi.BOX, capi.F32, 19, 4, "p2p"),    # 2-D fused exchange: faces are rows
+    ((4096, 512), 1, capi.STAR, capi.F64, 26, 6, "p2p"),
+    ((300, 128, 40), 1, capi.BOX, capi.F64, 3, 1, "nccl"),
+    ((300, 128, 40), 1, capi.BOX, capi.F64, 9, 2, "p2p"),
+    ((1000, 256), 2, capi.STAR, capi.F32, 11, 4, "p2p"),   # radius > 1: warp2dr, faces are r*k rows
+    ((1000, 256), 2, capi.STAR, capi.F32, 11, 4, "nccl"),
+    ((900, 200), 2, capi.BOX, capi.F32, 7, 2, "p2p"),      # 25-point box
+    ((640, 256), 3, capi.STAR, capi.F64, 5, 2, "p2p"),
+    ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "nccl"),  # 13-point star (tma3dr), NCCL exchange
+]
+for n_local, radius, shape, dtype, T, k, exch in CASES:
+    d = capi.make_desc(n_local, radius, shape, dtype, T, time_block=k)
     sw = slab.SlabSweep(d, rank, world, exchange=exch)
     sw.fill(capi.INIT_RANDOM, seed=3)
     sw.sweep(T)
@@ -38,14 +46,14 @@ for n_local, shape, dtype, T, k, exch in [((256, 200, 64), capi.STAR, capi.F64, 
     if rank == 0:
         n_full = list(n_local)
         n_full[-1] *= world
-        df = capi.make_desc(n_full, 1, shape, dtype, T, time_block=k)
+        df = capi.make_desc(n_full, radius, shape, dtype, T, time_block=k)
         g = sweep.DeviceGrids(df)
         g.fill(capi.INIT_RANDOM, seed=3)
         g.sweep(T)
         want = g.checksum()
         good = want == total
         ok &= good
-        print(f"n_local={n_local} shape={shape} dtype={dtype} T={T} k={k} world={world} exchange={exch}: "
+        print(f"n_local={n_local} r={radius} shape={shape} dtype={dtype} T={T} k={k} world={world} exchange={exch}: "
               f"{'bitwise identical' if good else 'MISMATCH'} ({want:#x} vs {total:#x})", flush=True)
         del g
     dist.barrier()
