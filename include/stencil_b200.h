@@ -303,7 +303,7 @@ int sb200_ipc_close(void* dev_ptr);
  * in ONE launch: the CTAs of the first and last z chunk are dispatched first and
  * push the face planes to the neighbours (peer stores + arrival signal).
  * Needs ghost == radius * max-steps-between-exchanges >= radius * steps and a
- * slab of at least 2*ghost planes (rows in 2-D); radius 1 only: the TMA3D family in 3-D, the
+ * slab of at least 2*ghost planes (rows in 2-D); the TMA3D family at radius 1 in 3-D, the whole
  * WARP2D family in 2-D (faces are rows, their owners warps — the reference's RMA kernel is the
  * 2-D case, stencil_rma.cpp:333-458).
  * *arrivals = face owners (CTAs in 3-D, warps in 2-D) per face of this launch (add it to
