@@ -321,6 +321,28 @@ int sb200_link_status(const uint32_t* flags_local, uint32_t words[SB200_LINK_FLA
  * wait_arrivals at 0. */
 int sb200_link_reset(uint32_t* flags_local);
 
+/* ---- device-resident sweep over the device group (one process, N GPUs) -----------------------
+ * The whole of a multi-GPU device-resident run in ONE call, for C and C++ hosts that have no
+ * process launcher: the grid of `desc` is cut into desc->ngpus (0 = all bound devices) equal
+ * slabs along the outermost axis, generated on the devices (init / seed as sb200_fill_device),
+ * swept desc->iterations steps with one linked launch per slab and fused block — the
+ * neighbours' buffers are reached through CUDA peer access inside the process — and digested.
+ * Then `repeats` further sweeps of the same length are timed.  This is the reference's RMA
+ * method (tiles resident on the accelerator, neighbours exchanging halos directly, main memory
+ * out of the loop: stencil_rma.cpp:333-458) across GPUs.  Needs a kernel family with the fused
+ * exchange for ngpus > 1 (WARP2D, TMA3D at radius 1), an outermost extent divisible by ngpus
+ * and slabs of at least 2 * radius * time_block planes.  The digest equals
+ * sb200_checksum_device's of the same grid swept on one GPU, bit for bit. */
+typedef struct sb200_group_result {
+    double sweep_ms;     /* device time of ONE timed sweep of `iterations` steps (max over GPUs) */
+    uint64_t checksum;   /* whole-grid digest after the first `iterations` steps */
+    uint32_t ngpus, time_block, launches;
+    int32_t kernel;      /* sb200_kernel family */
+    int32_t exchange;    /* 0: none (one GPU), 1: fused peer stores */
+} sb200_group_result;
+int sb200_group_sweep(const sb200_desc* desc, int init, uint64_t seed, uint32_t repeats,
+                      sb200_group_result* res);
+
 /* What the library WOULD do for `steps` steps of this descriptor on a whole grid of
  * a device with `sm_count` SMs — pure host logic, no device needed (tests, tuning,
  * the experiment driver's block-size column).  Meaning of the geometry fields:

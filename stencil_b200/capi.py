@@ -29,7 +29,7 @@ SYMBOLS = [
     "sb200_host_register", "sb200_host_unregister", "sb200_plan", "sb200_pipeline_schedule",
     "sb200_init_multi", "sb200_group_size", "sb200_prepare", "sb200_slab_plan_for",
     "sb200_pipeline_schedule_slab", "sb200_link_reset", "sb200_host_alloc_for", "sb200_host_place",
-    "sb200_checksum_device_noalloc",
+    "sb200_checksum_device_noalloc", "sb200_group_sweep",
 ]
 NOALLOC_MAX_POINTS = 8192 * 16384
 MAX_GPUS = 16
@@ -92,6 +92,12 @@ class SlabPlan(ctypes.Structure):
     _fields_ = [("ngpus_used", ctypes.c_uint32), ("deep_halo", ctypes.c_uint32), ("slab", _Slab * MAX_GPUS)]
 
 
+class GroupResult(ctypes.Structure):
+    _fields_ = [("sweep_ms", ctypes.c_double), ("checksum", ctypes.c_uint64), ("ngpus", ctypes.c_uint32),
+                ("time_block", ctypes.c_uint32), ("launches", ctypes.c_uint32), ("kernel", ctypes.c_int32),
+                ("exchange", ctypes.c_int32)]
+
+
 class PipeOp(ctypes.Structure):
     _fields_ = [
         ("kind", ctypes.c_int32), ("stream", ctypes.c_int32), ("parallelogram", ctypes.c_int32),
@@ -127,6 +133,7 @@ def lib() -> ctypes.CDLL:
         L.sb200_init_multi.argtypes = [i32, ctypes.POINTER(i32)]
         L.sb200_group_size.restype = i32
         L.sb200_prepare.argtypes = [dp]
+        L.sb200_group_sweep.argtypes = [dp, i32, u64, u32, ctypes.POINTER(GroupResult)]
         L.sb200_slab_plan_for.argtypes = [dp, i32, ctypes.POINTER(SlabPlan)]
         L.sb200_pipeline_schedule_slab.argtypes = [dp, i32, i32, ctypes.POINTER(PipeOp), u32,
                                                    ctypes.POINTER(u32), ctypes.POINTER(u32)]

@@ -856,6 +856,10 @@ int sb200_link_reset(uint32_t* flags_local) {
     return SB200_OK;
 }
 
+static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary, int hi_is_boundary,
+                            const void* a, void* b, uint32_t steps, const sb200_slab_link* link, void* stream,
+                            uint32_t* arrivals);
+
 int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary,
                             int hi_is_boundary, const void* a, void* b, uint32_t steps,
                             const sb200_slab_link* link, void* stream, uint32_t* arrivals) {
@@ -863,6 +867,13 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     if (!a || !b || !link) return fail(SB200_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
+    return slab_linked_impl(desc, ghost, lo_is_boundary, hi_is_boundary, a, b, steps, link, stream, arrivals);
+}
+
+// On the calling thread's current State / device; the caller holds g_mu.
+static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_boundary, int hi_is_boundary,
+                            const void* a, void* b, uint32_t steps, const sb200_slab_link* link, void* stream,
+                            uint32_t* arrivals) {
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
     const bool w2d = c.kernel == SB200_KERNEL_WARP2D;
@@ -933,6 +944,9 @@ int sb200_sweep_slab_linked(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     return launch_tma3d<float>((const float*)a, (float*)b, desc->dtype, g, t3_shape(desc), dom, (int)steps, ob, oe, st, L);
 }
 
+static int fill_impl(const sb200_desc* desc, uint32_t ghost, void* grid, int init, uint64_t seed, uint64_t z_offset,
+                     uint64_t z_total, cudaStream_t st);
+
 int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int init, uint64_t seed,
                       uint64_t z_offset, uint64_t z_total, void* stream) {
     if (int rc = validate(desc)) return rc;
@@ -940,13 +954,17 @@ int sb200_fill_device(const sb200_desc* desc, uint32_t ghost, void* grid, int in
     if (init != SB200_INIT_REF && init != SB200_INIT_RANDOM) return fail(SB200_ERR_INVALID, "bad init %d", init);
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
+    return fill_impl(desc, ghost, grid, init, seed, z_offset, z_total, (cudaStream_t)stream);
+}
+
+static int fill_impl(const sb200_desc* desc, uint32_t ghost, void* grid, int init, uint64_t seed, uint64_t z_offset,
+                     uint64_t z_total, cudaStream_t st) {
     const Grid g = make_grid(desc, ghost);
     long long gn[3] = {g.n[0], g.n[1], g.n[2]};
     if (z_total) gn[desc->ndim - 1] = (long long)z_total;
     const long long total = g.elems();
     long long blocks = (total + 255) / 256;
     if (blocks > DS().sm_count * 32) blocks = DS().sm_count * 32;
-    cudaStream_t st = (cudaStream_t)stream;
     if (desc->dtype == SB200_F64)
         fill_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((double*)grid, g, init == SB200_INIT_RANDOM, seed, gn[0], gn[1], gn[2], (long long)z_offset);
     else
@@ -1415,16 +1433,23 @@ int sb200_download(const sb200_desc* desc, uint32_t ghost, const void* dev, void
     return copy_grid(desc, ghost, dev, host, false, false, (cudaStream_t)stream);
 }
 
+static int checksum_impl(const sb200_desc* desc, uint32_t ghost, const void* grid, uint64_t z_offset, uint64_t z_total,
+                         cudaStream_t st, uint64_t* out);
+
 int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* grid, uint64_t z_offset,
                           uint64_t z_total, void* stream, uint64_t* out) {
     if (int rc = validate(desc)) return rc;
     if (!grid || !out) return fail(SB200_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> lk(g_mu);
     if (int rc = ensure_ready()) return rc;
+    return checksum_impl(desc, ghost, grid, z_offset, z_total, (cudaStream_t)stream, out);
+}
+
+static int checksum_impl(const sb200_desc* desc, uint32_t ghost, const void* grid, uint64_t z_offset, uint64_t z_total,
+                         cudaStream_t st, uint64_t* out) {
     const Grid g = make_grid(desc, ghost);
     long long gn[3] = {g.n[0], g.n[1], g.n[2]};
     if (z_total) gn[desc->ndim - 1] = (long long)z_total;
-    cudaStream_t st = (cudaStream_t)stream;
     CU_TRY(cudaMemsetAsync(DS().d_acc, 0, sizeof(unsigned long long), st));
     const long long total = g.n[0] * g.n[1] * g.n[2];
     long long blocks = (total + 255) / 256;
@@ -1439,6 +1464,206 @@ int sb200_checksum_device(const sb200_desc* desc, uint32_t ghost, const void* gr
     CU_TRY(cudaStreamSynchronize(st));
     *out = (uint64_t)h;
     return SB200_OK;
+}
+
+// ---- device-resident sweep over the device group: one process, N GPUs, no torch -------------
+// The C++ spelling of what stencil_b200/slab.py does with one process per GPU: slabs of the
+// outermost axis with ghost = r*k planes / rows, one linked launch per slab and fused block
+// (peer stores over NVLink + arrival counters, slablink.cuh).  Inside one process the
+// neighbours' buffers are reachable after cudaDeviceEnablePeerAccess — no IPC handles — and one
+// host thread issues every launch (they are asynchronous; block b of every slab is enqueued
+// before block b+1 of any, which is the order the arrival counters assume).
+struct GroupSlab {
+    State* st = nullptr;
+    void* buf[2] = {nullptr, nullptr};
+    uint32_t* flags = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    uint32_t arrivals = 0;
+};
+
+static void group_release(std::vector<GroupSlab>& slabs) {
+    for (GroupSlab& gs : slabs) {
+        if (!gs.st) continue;
+        tls_state = gs.st;
+        cudaSetDevice(gs.st->device);
+        cudaDeviceSynchronize();
+        for (void* p : gs.buf)
+            if (p) {
+                for (size_t i = 0; i < gs.st->maps.size();)
+                    if (gs.st->maps[i].key.ptr == p) gs.st->maps.erase(gs.st->maps.begin() + (long)i); else ++i;
+                cudaFree(p);
+            }
+        if (gs.flags) cudaFree(gs.flags);
+        if (gs.e0) cudaEventDestroy(gs.e0);
+        if (gs.e1) cudaEventDestroy(gs.e1);
+    }
+    tls_state = nullptr;
+    if (!g_group.empty()) cudaSetDevice(g_group[0]->device);
+}
+
+static int group_sweep_impl(const sb200_desc* desc, int init, uint64_t seed, uint32_t repeats, int G,
+                            std::vector<GroupSlab>& slabs, sb200_group_result* res) {
+    const Choice c = choose(desc);
+    if (int rc = check_choice(desc, c)) return rc;
+    const int nd = desc->ndim;
+    const uint64_t n_outer = desc->n[nd - 1];
+    const uint32_t T = desc->iterations, r = desc->radius;
+    memset(res, 0, sizeof *res);
+    res->ngpus = (uint32_t)G;
+    res->kernel = c.kernel;
+    res->time_block = (uint32_t)c.k;
+    sb200_desc sd = *desc;
+    uint32_t ghost = 0;
+    if (G > 1) {
+        const bool linkable = c.kernel == SB200_KERNEL_WARP2D || (c.kernel == SB200_KERNEL_TMA3D && r == 1);
+        if (!linkable)
+            return fail(SB200_ERR_UNSUPPORTED, "the fused halo exchange needs the WARP2D family or the TMA3D family at "
+                                               "radius 1; this descriptor runs on one GPU only");
+        if (n_outer % (uint64_t)G) return fail(SB200_ERR_INVALID, "outermost extent %llu is not a multiple of %d GPUs",
+                                               (unsigned long long)n_outer, G);
+        sd.n[nd - 1] = n_outer / (uint64_t)G;
+        ghost = r * (uint32_t)c.k;
+        if (sd.n[nd - 1] < 2ull * ghost)
+            return fail(SB200_ERR_INVALID, "slabs of %llu planes are thinner than two ghost zones (%u each)",
+                        (unsigned long long)sd.n[nd - 1], ghost);
+        res->exchange = 1;
+    }
+    const Grid g = make_grid(&sd, ghost);
+    const size_t bytes = (size_t)g.elems() * esize(sd.dtype);
+    // allocate, map the neighbours, fill
+    for (int i = 0; i < G; ++i) {
+        GroupSlab& gs = slabs[(size_t)i];
+        gs.st = g_group[(size_t)i];
+        tls_state = gs.st;
+        CU_TRY(cudaSetDevice(gs.st->device));
+        for (int nb : {i - 1, i + 1})
+            if (nb >= 0 && nb < G && g_group[(size_t)nb]->device != gs.st->device) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(g_group[(size_t)nb]->device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                    return fail(SB200_ERR_CUDA, "no peer access from GPU %d to GPU %d: %s", gs.st->device,
+                                g_group[(size_t)nb]->device, cudaGetErrorString(e));
+                cudaGetLastError();
+            }
+        for (void*& p : gs.buf) {
+            CU_TRY(cudaMalloc(&p, bytes));
+            CU_TRY(cudaMemsetAsync(p, 0, bytes, 0));
+        }
+        CU_TRY(cudaMalloc((void**)&gs.flags, sizeof(uint32_t) * SB200_LINK_FLAG_WORDS));
+        CU_TRY(cudaMemsetAsync(gs.flags, 0, sizeof(uint32_t) * SB200_LINK_FLAG_WORDS, 0));
+        CU_TRY(cudaEventCreate(&gs.e0));
+        CU_TRY(cudaEventCreate(&gs.e1));
+    }
+    auto for_each = [&](auto&& fn) -> int {
+        for (int i = 0; i < G; ++i) {
+            tls_state = slabs[(size_t)i].st;
+            CU_TRY(cudaSetDevice(slabs[(size_t)i].st->device));
+            if (int rc = fn(i, slabs[(size_t)i])) return rc;
+        }
+        return SB200_OK;
+    };
+    auto sync_all = [&]() { return for_each([](int, GroupSlab&) { CU_TRY(cudaDeviceSynchronize()); return (int)SB200_OK; }); };
+    const uint64_t off_unit = sd.n[nd - 1], z_total = G > 1 ? n_outer : 0;
+    auto fill = [&]() {
+        return for_each([&](int i, GroupSlab& gs) {
+            const uint64_t off = G > 1 ? off_unit * (uint64_t)i : 0;
+            if (int rc = fill_impl(&sd, ghost, gs.buf[0], init, seed, off, z_total, 0)) return rc;
+            return fill_impl(&sd, ghost, gs.buf[1], SB200_INIT_REF, 0, off, z_total, 0);
+        });
+    };
+    int cur = 0;
+    uint32_t launches = 0;
+    auto sweep_T = [&]() -> int {
+        if (G == 1) {
+            tls_state = slabs[0].st;
+            CU_TRY(cudaSetDevice(slabs[0].st->device));
+            int in_b = 0;
+            uint32_t nl = 0;
+            if (int rc = sweep_impl(&sd, 0, 1, 1, slabs[0].buf[cur], slabs[0].buf[cur ^ 1], T, 0, &in_b, &nl, nullptr, nullptr))
+                return rc;
+            if (in_b) cur ^= 1;
+            launches += nl;
+            return SB200_OK;
+        }
+        for (uint32_t done = 0; done < T;) {
+            const uint32_t k = T - done < (uint32_t)c.k ? T - done : (uint32_t)c.k;
+            if (int rc = for_each([&](int i, GroupSlab& gs) {
+                    sb200_slab_link lk = {};
+                    lk.peer_dst_lo = i > 0 ? slabs[(size_t)i - 1].buf[cur ^ 1] : nullptr;
+                    lk.peer_dst_hi = i + 1 < G ? slabs[(size_t)i + 1].buf[cur ^ 1] : nullptr;
+                    lk.flags_local = gs.flags;
+                    lk.flags_lo = i > 0 ? slabs[(size_t)i - 1].flags : nullptr;
+                    lk.flags_hi = i + 1 < G ? slabs[(size_t)i + 1].flags : nullptr;
+                    lk.wait_arrivals = gs.arrivals;
+                    uint32_t arr = 0;
+                    if (int rc = slab_linked_impl(&sd, ghost, i == 0, i + 1 == G, gs.buf[cur], gs.buf[cur ^ 1], k, &lk, nullptr, &arr))
+                        return rc;
+                    gs.arrivals += arr;
+                    ++launches;
+                    return (int)SB200_OK;
+                }))
+                return rc;
+            cur ^= 1;
+            done += k;
+        }
+        return SB200_OK;
+    };
+    if (int rc = fill()) return rc;
+    if (int rc = sync_all()) return rc;
+    // the digest after exactly T steps from the initial condition
+    if (int rc = sweep_T()) return rc;
+    if (int rc = sync_all()) return rc;
+    uint64_t total = 0;
+    if (int rc = for_each([&](int i, GroupSlab& gs) {
+            uint64_t part = 0;
+            if (int rc = checksum_impl(&sd, ghost, gs.buf[cur], G > 1 ? off_unit * (uint64_t)i : 0, z_total, 0, &part)) return rc;
+            total += part;
+            if (G > 1) {
+                uint32_t words[SB200_LINK_FLAG_WORDS];
+                CU_TRY(cudaMemcpy(words, gs.flags, sizeof words, cudaMemcpyDeviceToHost));
+                if (words[2]) return fail(SB200_ERR_CUDA, "GPU %d: a fused halo exchange timed out waiting for a neighbour", gs.st->device);
+            }
+            return (int)SB200_OK;
+        }))
+        return rc;
+    res->checksum = total;
+    res->launches = launches;
+    // timed: `repeats` further sweeps of T steps, device time = max over the GPUs
+    if (repeats) {
+        if (int rc = for_each([](int, GroupSlab& gs) { CU_TRY(cudaEventRecord(gs.e0, 0)); return (int)SB200_OK; })) return rc;
+        for (uint32_t rep = 0; rep < repeats; ++rep)
+            if (int rc = sweep_T()) return rc;
+        if (int rc = for_each([](int, GroupSlab& gs) { CU_TRY(cudaEventRecord(gs.e1, 0)); return (int)SB200_OK; })) return rc;
+        if (int rc = sync_all()) return rc;
+        for (GroupSlab& gs : slabs) {
+            float ms = 0;
+            CU_TRY(cudaEventElapsedTime(&ms, gs.e0, gs.e1));
+            if (ms > res->sweep_ms) res->sweep_ms = ms;
+            if (G > 1) {
+                uint32_t words[SB200_LINK_FLAG_WORDS];
+                CU_TRY(cudaSetDevice(gs.st->device));
+                CU_TRY(cudaMemcpy(words, gs.flags, sizeof words, cudaMemcpyDeviceToHost));
+                if (words[2]) return fail(SB200_ERR_CUDA, "GPU %d: a fused halo exchange timed out waiting for a neighbour", gs.st->device);
+            }
+        }
+        res->sweep_ms /= repeats;
+    }
+    return SB200_OK;
+}
+
+int sb200_group_sweep(const sb200_desc* desc, int init, uint64_t seed, uint32_t repeats, sb200_group_result* res) {
+    if (int rc = validate(desc)) return rc;
+    if (!res) return fail(SB200_ERR_INVALID, "null result");
+    if (init != SB200_INIT_REF && init != SB200_INIT_RANDOM) return fail(SB200_ERR_INVALID, "bad init %d", init);
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (int rc = ensure_ready()) return rc;
+    const int have = (int)g_group.size();
+    const int G = desc->ngpus == 0 ? have : (int)desc->ngpus;
+    if (G > have) return fail(SB200_ERR_INVALID, "ngpus = %d but %d device(s) are bound (sb200_init_multi)", G, have);
+    if (desc->ndim == 1 && G > 1) return fail(SB200_ERR_INVALID, "1-D grids are not slab-decomposed");
+    std::vector<GroupSlab> slabs((size_t)G);
+    const int rc = group_sweep_impl(desc, init, seed, repeats, G, slabs, res);
+    group_release(slabs);
+    return rc;
 }
 
 int sb200_checksum_device_noalloc(const sb200_desc* desc, uint32_t ghost, const void* grid, uint64_t z_offset,

@@ -41,6 +41,8 @@ public:
         int kernel = 0;
         int threads = 1;
         unsigned gpus = 1;       // GPUs the run was spread over
+        bool resident = false;   // device-resident run (sb200_group_sweep): no host grids were moved
+        unsigned long long checksum = 0;  // resident runs: digest of the final field
         bool pipelined = false;  // sweep_ms spans the whole overlapped upload/sweep/download pipeline
     };
 
@@ -83,6 +85,8 @@ private:
 
     template <class T> void initialize_typed();
     template <class T> auto run_typed(InputMethod method) -> std::chrono::steady_clock::duration;
+    auto run_resident() -> std::chrono::steady_clock::duration;
+    template <class T> unsigned long long naive_digest() const;
     template <class T> bool check_typed() const;
 };
 

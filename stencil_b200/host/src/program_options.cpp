@@ -38,6 +38,9 @@ auto ProgramOptions::parse(int argc, char** argv) -> std::optional<ProgramOption
     app.option("--seed", result.seed, "Seed of the random initial condition.", 1ull);
     app.option("--kernel", result.kernel, "CUDA kernel family: auto, generic, warp2d, tma3d, resident2d, line1d.", std::string("auto"));
     app.option("--gpus", result.gpus, "GPUs of this box one CUDA run is spread over (z-slabs; y-slabs in 2-D).", 1u);
+    app.flag("--resident", result.resident,
+             "CUDA: keep the grid on the GPUs for the whole run (generated there, swept, digested; with --gpus N "
+             "the slabs exchange halos directly over NVLink). The time is the sweep alone; -c compares digests.");
     app.flag("--block-as-tile", result.block_as_tile,
              "CUDA: use -b as the tile preference of the warp2d / tma3d kernels instead of the planner's choice.");
     app.option("--json", result.json_path, "Append one JSON record per method to this file.");

@@ -169,3 +169,61 @@ def test_block_hint_tile_preference_keeps_the_bits(gpu, n, shape, dtype, T, hint
     capi.check(gpu.sb200_run_host(ctypes.byref(d), ga.ctypes.data, gb.ctypes.data, ctypes.byref(t)))
     got = gb if T & 1 else ga
     assert np.array_equal(want.view(np.uint8), got.view(np.uint8))
+
+
+# ---- sb200_group_sweep: the device-resident multi-GPU run in one C-ABI call (no torch, no launcher) ----
+
+def _single_gpu_digest(n, r, shape, dtype, T):
+    d = capi.make_desc(n, r, shape, dtype, T)
+    g = sweep.DeviceGrids(d)
+    g.fill(capi.INIT_RANDOM, seed=6)
+    g.sweep(T)
+    return g.checksum()
+
+
+@pytest.mark.parametrize("n,r,shape,dtype,T,G", [
+    ((96, 80, 64), 1, capi.STAR, capi.F64, 7, 2),      # TMA3D, remainder block
+    ((70, 66, 96), 1, capi.BOX, capi.F32, 6, 4),       # 27-point, four slabs
+    ((300, 256), 1, capi.BOX, capi.F32, 13, 4),        # WARP2D rows
+    ((257, 240), 2, capi.STAR, capi.F64, 5, 2),        # warp2dr radius 2
+    ((200, 180), 2, capi.BOX, capi.F32, 6, 3),         # 25-point box, three slabs
+    ((64, 48, 40), 2, capi.BOX, capi.F64, 3, 1),       # generic kernel: one GPU only
+])
+def test_group_sweep_digest_equals_one_gpu(multi, n, r, shape, dtype, T, G):
+    L = multi(max(G, 2))
+    want = _single_gpu_digest(n, r, shape, dtype, T)
+    d = capi.make_desc(n, r, shape, dtype, T, ngpus=G)
+    res = capi.GroupResult()
+    capi.check(L.sb200_group_sweep(ctypes.byref(d), capi.INIT_RANDOM, 6, 2, ctypes.byref(res)))
+    assert res.ngpus == G and res.exchange == (1 if G > 1 else 0)
+    assert res.checksum == want, f"{res.checksum:#x} vs {want:#x}"
+    assert res.sweep_ms > 0 and res.launches > 0
+    # a second call (fresh buffers, counters from zero) gives the same digest
+    capi.check(L.sb200_group_sweep(ctypes.byref(d), capi.INIT_RANDOM, 6, 0, ctypes.byref(res)))
+    assert res.checksum == want
+
+
+def test_group_sweep_rejects_what_it_cannot_link(multi):
+    L = multi(2)
+    res = capi.GroupResult()
+    d = capi.make_desc((64, 48, 40), 2, capi.BOX, capi.F64, 3, ngpus=2)      # generic kernel has no fused exchange
+    assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_UNSUPPORTED
+    d = capi.make_desc((64, 48, 41), 1, capi.STAR, capi.F64, 3, ngpus=2)     # 41 planes over 2 GPUs
+    assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_INVALID
+    d = capi.make_desc((64, 48, 6), 1, capi.STAR, capi.F64, 3, ngpus=2)      # 3-plane slabs < 2 ghost zones
+    assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_INVALID
+    d = capi.make_desc((64, 48, 40), 1, capi.STAR, capi.F64, 3, ngpus=3)     # more than the group holds
+    assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_INVALID
+
+
+def test_cli_resident_mode_self_check(gpu):
+    """stencil_main --resident [--gpus N] -c: the grid lives on the GPUs; -c compares the device digest
+    with the digest of the host's naive loop."""
+    have = gpu.sb200_device_count()
+    g = 2 if have >= 2 else 1
+    for extra in (["--shape", "160,120,96", "--dtype", "f64", "-i", "7"], ["-s", "512", "--stencil", "box", "-i", "21"]):
+        r = subprocess.run([BIN, "-s", "1", "-b", "1", "--init", "random", "--resident", "--gpus", str(g), "-m", "CUDA", "-c"] + extra,
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert "The results of method CUDA is correct." in r.stdout and "bit-exact vs naive loop: yes" in r.stdout
+        assert "device-resident" in r.stdout and re.search(rf", {g} GPU", r.stdout)
