@@ -303,8 +303,8 @@ int sb200_ipc_close(void* dev_ptr);
  * in ONE launch: the CTAs of the first and last z chunk are dispatched first and
  * push the face planes to the neighbours (peer stores + arrival signal).
  * Needs ghost == radius * max-steps-between-exchanges >= radius * steps and a
- * slab of at least 2*ghost planes (rows in 2-D); the TMA3D family at radius 1 in 3-D, the whole
- * WARP2D family in 2-D (faces are rows, their owners warps — the reference's RMA kernel is the
+ * slab of at least 2*ghost planes (rows in 2-D); the TMA3D family in 3-D, the WARP2D family
+ * in 2-D (faces are rows, their owners warps — the reference's RMA kernel is the
  * 2-D case, stencil_rma.cpp:333-458).
  * *arrivals = face owners (CTAs in 3-D, warps in 2-D) per face of this launch (add it to
  * wait_arrivals). */
@@ -330,7 +330,7 @@ int sb200_link_reset(uint32_t* flags_local);
  * Then `repeats` further sweeps of the same length are timed.  This is the reference's RMA
  * method (tiles resident on the accelerator, neighbours exchanging halos directly, main memory
  * out of the loop: stencil_rma.cpp:333-458) across GPUs.  Needs a kernel family with the fused
- * exchange for ngpus > 1 (WARP2D, TMA3D at radius 1), an outermost extent divisible by ngpus
+ * exchange for ngpus > 1 (WARP2D, TMA3D), an outermost extent divisible by ngpus
  * and slabs of at least 2 * radius * time_block planes.  The digest equals
  * sb200_checksum_device's of the same grid swept on one GPU, bit for bit. */
 typedef struct sb200_group_result {

@@ -373,18 +373,31 @@ int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domai
 // 3-D star of radius 2 (13-point), one step per launch (tma3dr.cuh).
 template <class T>
 int launch_tma3dr(const T* in, T* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
-                  int prefer_chunk) {
+                  int prefer_chunk, const SlabLinkDev* link_in = nullptr) {
     using C = T3R<T, 2>;
     if (oe <= ob) return SB200_OK;
-    if (int rc = set_smem_attr_once(sweep_tma3dr_kernel<T, 2>, C::SMEM)) return rc;
+    const bool linked = link_in && (link_in->link_lo || link_in->link_hi);
+    if (int rc = linked ? set_smem_attr_once(sweep_tma3dr_kernel<T, 2, true>, C::SMEM)
+                        : set_smem_attr_once(sweep_tma3dr_kernel<T, 2, false>, C::SMEM))
+        return rc;
     const CUtensorMap* mp = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, C::BX, C::BY, false, &mp)) return rc;
     const CUtensorMap imap = *mp;
     if (int rc = get_tensor_map(out, dtype, g, C::VX, C::VY, true, &mp)) return rc;
     const CUtensorMap omap = *mp;
     const T3Plan p = t3r_plan<T, 2>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
-    sweep_tma3dr_kernel<T, 2><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
-        imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2));
+    if (linked) {
+        SlabLinkDev link = *link_in;
+        long long nc = p.nchunks;
+        if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
+        if (nc < 1) nc = 1;
+        link.nchunks = (int)nc;
+        sweep_tma3dr_kernel<T, 2, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
+            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2), link);
+    } else {
+        sweep_tma3dr_kernel<T, 2, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
+            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2), SlabLinkDev{});
+    }
     CU_TRY(cudaGetLastError());
     return SB200_OK;
 }
@@ -877,8 +890,8 @@ static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
     const Choice c = choose(desc);
     if (int rc = check_choice(desc, c)) return rc;
     const bool w2d = c.kernel == SB200_KERNEL_WARP2D;
-    if (!w2d && (c.kernel != SB200_KERNEL_TMA3D || desc->radius != 1))
-        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the WARP2D family or the TMA3D family at radius 1");
+    if (!w2d && c.kernel != SB200_KERNEL_TMA3D)
+        return fail(SB200_ERR_UNSUPPORTED, "linked slab sweeps need the WARP2D or the TMA3D family");
     if (steps < 1 || (int)steps > c.max_k)
         return fail(SB200_ERR_INVALID, "linked sweep fuses 1..%d steps (got %u)", c.max_k, steps);
     const Grid g = make_grid(desc, ghost);
@@ -923,6 +936,14 @@ static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
             CU_TRY(launch_warp2d<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
         }
         return SB200_OK;
+    }
+    if (g.r > 1) {  // 13-point star (tma3dr.cuh)
+        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan<double, 2>(g.n[0], g.n[1], 1, DS().sm_count)
+                                                  : t3r_plan<float, 2>(g.n[0], g.n[1], 1, DS().sm_count);
+        if (arrivals) *arrivals = (uint32_t)(p.ntx * p.nty);
+        if (desc->dtype == SB200_F64)
+            return launch_tma3dr<double>((const double*)a, (double*)b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);
+        return launch_tma3dr<float>((const float*)a, (float*)b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);
     }
     int ntx, nty;
     if (desc->dtype == SB200_F64) {
@@ -1515,10 +1536,10 @@ static int group_sweep_impl(const sb200_desc* desc, int init, uint64_t seed, uin
     sb200_desc sd = *desc;
     uint32_t ghost = 0;
     if (G > 1) {
-        const bool linkable = c.kernel == SB200_KERNEL_WARP2D || (c.kernel == SB200_KERNEL_TMA3D && r == 1);
+        const bool linkable = c.kernel == SB200_KERNEL_WARP2D || c.kernel == SB200_KERNEL_TMA3D;
         if (!linkable)
-            return fail(SB200_ERR_UNSUPPORTED, "the fused halo exchange needs the WARP2D family or the TMA3D family at "
-                                               "radius 1; this descriptor runs on one GPU only");
+            return fail(SB200_ERR_UNSUPPORTED, "the fused halo exchange needs the WARP2D or the TMA3D family; this "
+                                               "descriptor runs on one GPU only");
         if (n_outer % (uint64_t)G) return fail(SB200_ERR_INVALID, "outermost extent %llu is not a multiple of %d GPUs",
                                                (unsigned long long)n_outer, G);
         sd.n[nd - 1] = n_outer / (uint64_t)G;

@@ -51,11 +51,14 @@ __device__ __forceinline__ T t3r_at(const T (&v)[PXV]) {
     else return __shfl_down_sync(0xffffffffu, v[EL], LANE);
 }
 
-template <class T, int R>
+// LINKED: the slab link of tma3d.cuh / slablink.cuh (faces are g = R planes; the CTAs of the first
+// / last z chunk own them, are dispatched first, acquire the neighbours' arrival counter before
+// their first TMA load and push their face planes after the z stream).
+template <class T, int R, bool LINKED = false>
 __global__ void __launch_bounds__(T3R<T, R>::THREADS, 1)
 sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap omap,
                     T* __restrict__ out, Grid g, long long ob, long long oe, int ntx, int nty, int chunk_planes,
-                    T avg) {
+                    T avg, const SlabLinkDev link) {
     using C = T3R<T, R>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
     static_assert(R == 2, "only the 13-point star is instantiated");
@@ -70,9 +73,13 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     const int tiles = ntx * nty;
     const int tile = (int)(blockIdx.x % (unsigned)tiles);
     const int tix = tile % ntx, tiy = tile / ntx;
-    const int chunk = (int)(blockIdx.x / (unsigned)tiles);
-    const long long zb = ob + (long long)chunk * chunk_planes;
-    const long long ze = zb + chunk_planes < oe ? zb + chunk_planes : oe;
+    int chunk = (int)(blockIdx.x / (unsigned)tiles);
+    if (LINKED && link.link_hi) chunk = chunk == 0 ? link.nchunks - 1 : chunk - 1;  // the last chunk first
+    const bool is_lo = LINKED && link.link_lo && chunk == 0;
+    const bool is_hi = LINKED && link.link_hi && chunk == link.nchunks - 1;
+    const long long zb = LINKED ? ob + (oe - ob) * chunk / link.nchunks : ob + (long long)chunk * chunk_planes;
+    const long long ze = LINKED ? ob + (oe - ob) * (chunk + 1) / link.nchunks
+                                : (zb + chunk_planes < oe ? zb + chunk_planes : oe);
     const long long gx0 = (long long)tix * C::VX - C::HLX;
     const long long gy0 = (long long)tiy * C::VY - R;
     const long long z_first = zb - R;
@@ -81,6 +88,11 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
     if (tid == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (LINKED && (is_lo || is_hi) && link.wait_value != 0) {
+            if (is_lo) link_wait(link.wait_lo, link.wait_value, link.err_flag);
+            if (is_hi) link_wait(link.wait_hi, link.wait_value, link.err_flag);
+            asm volatile("fence.proxy.async.global;" ::: "memory");  // TMA reads go through the async proxy
+        }
     }
     __syncthreads();
     const int cx = (int)(gx0 + g.ox), cy = (int)(gy0 + g.oy), cz0 = (int)(z_first + g.oz);
@@ -205,6 +217,47 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         if constexpr (R > 1) step(IC<1 % R>{}, j + 1);
     }
     if (tid == 0) tma_store_wait_all();
+    if (LINKED && (is_lo || is_hi)) {
+        // face push (as in tma3d.cuh): this CTA's TMA stores are complete (thread 0 waited, then
+        // the barrier and the proxy fence); every thread copies its part of the face planes into
+        // the neighbour's ghost planes, then thread 0 publishes them and counts the CTA in
+        __syncthreads();
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        const long long plane_stride = g.pitch_x * g.pitch_y;
+        T* home = out + g.idx(gx, gy, 0);
+        const bool col_in = gx < g.n[0], col_full = gx + PXV <= g.n[0];
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) {
+            if (side == 0 ? !is_lo : !is_hi) continue;
+            const long long z0 = side == 0 ? 0 : g.n[2] - link.face_planes;
+            const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
+                                     (side == 0 ? link.shift_lo : link.shift_hi);
+#pragma unroll 1
+            for (int p = 0; p < link.face_planes; ++p) {
+                T* src = home + (z0 + p) * plane_stride;
+#pragma unroll
+                for (int i = 0; i < PY; ++i) {
+                    if ((s_rows & (1u << i)) && col_in && gy + i < g.n[1]) {
+                        if (col_full) {
+                            T v[PXV];
+                            VecN<T, PXV>::ldcg(src + i * g.pitch_x, v);
+                            VecN<T, PXV>::st(src + rdelta + i * g.pitch_x, v);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < PXV; ++k)
+                                if (gx + k < g.n[0]) src[rdelta + i * g.pitch_x + k] = __ldcg(src + i * g.pitch_x + k);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
+            if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
+        }
+    }
 }
 
 template <class T, int R>

@@ -244,7 +244,7 @@ class SlabSweep:
         if exchange not in ("p2p", "nccl"):
             raise ValueError(f"exchange must be 'auto', 'p2p' or 'nccl' (got {exchange!r})")
         if exchange == "p2p" and not self._linkable():
-            raise ValueError("exchange='p2p' needs the WARP2D family (2-D) or the TMA3D family at radius 1 (3-D)")
+            raise ValueError("exchange='p2p' needs the WARP2D family (2-D) or the TMA3D family (3-D)")
         self.exchange = exchange if world > 1 else "none"
         p2p = self.exchange == "p2p"
         factory = engine_factory or (lambda d, g: CudaEngine(d, g, _current_device(), exportable=p2p))
@@ -279,7 +279,7 @@ class SlabSweep:
 
     def _linkable(self) -> bool:
         """Kernel families with the fused peer-store exchange (sb200_sweep_slab_linked)."""
-        return self.kernel == capi.KERNEL_WARP2D or (self.kernel == capi.KERNEL_TMA3D and self.r == 1)
+        return self.kernel in (capi.KERNEL_WARP2D, capi.KERNEL_TMA3D)
 
     def _all_ok(self, ok: bool) -> bool:
         """Logical AND of `ok` over all ranks (engines that are not CUDA-backed skip it)."""

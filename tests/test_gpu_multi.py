@@ -187,6 +187,7 @@ def _single_gpu_digest(n, r, shape, dtype, T):
     ((300, 256), 1, capi.BOX, capi.F32, 13, 4),        # WARP2D rows
     ((257, 240), 2, capi.STAR, capi.F64, 5, 2),        # warp2dr radius 2
     ((200, 180), 2, capi.BOX, capi.F32, 6, 3),         # 25-point box, three slabs
+    ((96, 80, 48), 2, capi.STAR, capi.F64, 5, 3),      # 13-point star (tma3dr), three slabs
     ((64, 48, 40), 2, capi.BOX, capi.F64, 3, 1),       # generic kernel: one GPU only
 ])
 def test_group_sweep_digest_equals_one_gpu(multi, n, r, shape, dtype, T, G):

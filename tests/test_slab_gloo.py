@@ -179,15 +179,14 @@ def test_exchange_mode_selection():
     d3r = capi.make_desc((8, 8, 16), radius=2)
     d2g = capi.make_desc((8, 32), radius=3, shape=capi.BOX)
     assert slab.SlabSweep(d3, 0, 1, engine_factory=OracleEngine).exchange == "none"
-    # the fused exchange exists for the WARP2D family (rows) and for TMA3D at radius 1 (planes)
+    # the fused exchange exists for the WARP2D family (rows) and the TMA3D family (planes)
     assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p").exchange == "p2p"
     assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"
     assert slab.SlabSweep(d2r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"
-    assert slab.SlabSweep(d3r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"   # 13-point: tma3dr
+    assert slab.SlabSweep(d3r, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "p2p"    # 13-point: tma3dr
     assert slab.SlabSweep(d2g, 0, 2, engine_factory=OracleEngine, dist=dist).exchange == "nccl"   # generic kernel
-    for d in (d3r, d2g):
-        with pytest.raises(ValueError):
-            slab.SlabSweep(d, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
+    with pytest.raises(ValueError):
+        slab.SlabSweep(d2g, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p")
     with pytest.raises(ValueError):
         slab.SlabSweep(d3, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="bogus")
 

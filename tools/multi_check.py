@@ -29,7 +29,9 @@ CASES = [  # n_local, radius, shape, dtype, T, k, exchange
     ((1000, 256), 2, capi.STAR, capi.F32, 11, 4, "nccl"),
     ((900, 200), 2, capi.BOX, capi.F32, 7, 2, "p2p"),      # 25-point box
     ((640, 256), 3, capi.STAR, capi.F64, 5, 2, "p2p"),
-    ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "nccl"),  # 13-point star (tma3dr), NCCL exchange
+    ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "nccl"),  # 13-point star (tma3dr)
+    ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "p2p"),
+    ((200, 160, 48), 2, capi.BOX, capi.F32, 3, 1, "nccl"),   # 125-point box: generic kernel, NCCL only
 ]
 for n_local, radius, shape, dtype, T, k, exch in CASES:
     d = capi.make_desc(n_local, radius, shape, dtype, T, time_block=k)
