@@ -288,7 +288,8 @@ def config5_leg(args, torch, dist, capi, slab, rank, world, local, barrier):
             "efficiency_at_matched_clock": (eff * C5_BASE["sm_mhz"] / clocks["sm_mhz"]
                                             if clocks and clocks.get("sm_mhz") and C5_BASE["sm_mhz"] else None),
             "note": "efficiency = value / N / base_value; the matched-clock figure rescales by the median SM "
-                    "clock of the two runs (the kernels are SM-bound, profiles/r02a_sm_bound_probe.log)"}
+                    "clock of the two runs (under the 1000 W cap the long 1-GPU run clocks lower than the short "
+                    "N-GPU runs, and throughput follows the clock: profiles/README.md r02)"}
     return out
 
 
