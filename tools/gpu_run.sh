@@ -48,6 +48,7 @@ task() {
       for ex in p2p nccl; do timeout 300 $TR --nproc-per-node $n --master-port 29613 tools/config4.py --exchange $ex 2>&1 | grep '^{'; done | tee gpurun_out/config4_n$n.log
       timeout 300 python tools/config4.py 2>&1 | grep '^{' | tee -a gpurun_out/config4_n$n.log ;;
     n8) nvidia-smi topo -m > gpurun_out/topo_n8.txt 2>&1; lscpu | grep -E "NUMA|Socket|Model name|^CPU\(s\)" > gpurun_out/lscpu_n8.txt 2>&1
+      [ -x tools/pcie_probe ] || nvcc -O2 -std=c++17 -gencode arch=compute_100a,code=sm_100a -cudart static -o tools/pcie_probe tools/pcie_probe.cu
       timeout 300 tools/pcie_probe 512 > gpurun_out/pcie_probe_n8.log 2>&1; echo "probe rc=$?"
       task torchbench 8 n8
       timeout 600 stencil_b200/host/build/bin/stencil_main -s 1 -i 8 -b 1 --shape 1024,1024,2048 --dtype f64 --init random --gpus 8 -R 2 -m CUDA -c > gpurun_out/cli_config5_n8.log 2>&1; echo "cli rc=$?"
