@@ -370,36 +370,56 @@ int launch_tma3d(const T* in, T* out, int dtype, const Grid& g, int shape, Domai
     }
 }
 
-// 3-D star of radius 2 (13-point), one step per launch (tma3dr.cuh).
-template <class T>
-int launch_tma3dr(const T* in, T* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
-                  int prefer_chunk, const SlabLinkDev* link_in = nullptr) {
-    using C = T3R<T, 2>;
+// 3-D star of radius 2..4 (13-, 19-, 25-point), one step per launch (tma3dr.cuh).
+template <class T, int R>
+int launch_tma3dr_r(const T* in, T* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
+                    int prefer_chunk, const SlabLinkDev* link_in) {
+    using C = T3R<T, R>;
     if (oe <= ob) return SB200_OK;
     const bool linked = link_in && (link_in->link_lo || link_in->link_hi);
-    if (int rc = linked ? set_smem_attr_once(sweep_tma3dr_kernel<T, 2, true>, C::SMEM)
-                        : set_smem_attr_once(sweep_tma3dr_kernel<T, 2, false>, C::SMEM))
+    if (int rc = linked ? set_smem_attr_once(sweep_tma3dr_kernel<T, R, true>, C::SMEM)
+                        : set_smem_attr_once(sweep_tma3dr_kernel<T, R, false>, C::SMEM))
         return rc;
     const CUtensorMap* mp = nullptr;
     if (int rc = get_tensor_map(in, dtype, g, C::BX, C::BY, false, &mp)) return rc;
     const CUtensorMap imap = *mp;
     if (int rc = get_tensor_map(out, dtype, g, C::VX, C::VY, true, &mp)) return rc;
     const CUtensorMap omap = *mp;
-    const T3Plan p = t3r_plan<T, 2>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
+    const T3Plan p = t3r_plan<T, R>(g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
+    const T avg = Avg<T>::value(STAR, 3, R);
     if (linked) {
         SlabLinkDev link = *link_in;
         long long nc = p.nchunks;
         if (nc > (oe - ob) / link.face_planes) nc = (oe - ob) / link.face_planes;
         if (nc < 1) nc = 1;
         link.nchunks = (int)nc;
-        sweep_tma3dr_kernel<T, 2, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
-            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2), link);
+        sweep_tma3dr_kernel<T, R, true><<<(unsigned)(nc * p.ntx * p.nty), C::THREADS, C::SMEM, st>>>(
+            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, link);
     } else {
-        sweep_tma3dr_kernel<T, 2, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
-            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, Avg<T>::value(STAR, 3, 2), SlabLinkDev{});
+        sweep_tma3dr_kernel<T, R, false><<<(unsigned)p.blocks, C::THREADS, C::SMEM, st>>>(
+            imap, omap, out, g, ob, oe, p.ntx, p.nty, p.chunk_planes, avg, SlabLinkDev{});
     }
     CU_TRY(cudaGetLastError());
     return SB200_OK;
+}
+
+template <class T>
+int launch_tma3dr(const T* in, T* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
+                  int prefer_chunk, const SlabLinkDev* link = nullptr) {
+    switch (g.r) {
+        case 2: return launch_tma3dr_r<T, 2>(in, out, dtype, g, ob, oe, st, prefer_chunk, link);
+        case 3: return launch_tma3dr_r<T, 3>(in, out, dtype, g, ob, oe, st, prefer_chunk, link);
+        case 4: return launch_tma3dr_r<T, 4>(in, out, dtype, g, ob, oe, st, prefer_chunk, link);
+    }
+    return fail(SB200_ERR_INVALID, "TMA3D star kernel: radius %d out of range", g.r);
+}
+
+// tiles / chunks of the radius-R star kernel (host logic)
+template <class T>
+T3Plan t3r_plan_any(int r, long long nx, long long ny, long long planes, int sm_count, int prefer) {
+    return r == 2 ? t3r_plan<T, 2>(nx, ny, planes, sm_count, prefer)
+           : r == 3 ? t3r_plan<T, 3>(nx, ny, planes, sm_count, prefer)
+                    : t3r_plan<T, 4>(nx, ny, planes, sm_count, prefer);
 }
 
 // Kernel family + fused depth for a descriptor.
@@ -415,9 +435,9 @@ bool warp2d_supports(const sb200_desc* d) {
                             (d->shape == SB200_BOX && d->radius == 2));
 }
 
-// TMA3D family: radius 1 star / box (tma3d.cuh), radius 2 star (tma3dr.cuh).
+// TMA3D family: radius 1 star / box (tma3d.cuh), radius 2..4 star (tma3dr.cuh).
 bool tma3d_supports(const sb200_desc* d) {
-    return d->ndim == 3 && (d->radius == 1 || (d->radius == 2 && d->shape == SB200_STAR));
+    return d->ndim == 3 && (d->radius == 1 || (d->radius >= 2 && d->radius <= 4 && d->shape == SB200_STAR));
 }
 
 Choice choose(const sb200_desc* d) {
@@ -449,7 +469,7 @@ int check_choice(const sb200_desc* d, const Choice& c) {
     if (c.kernel == SB200_KERNEL_LINE1D && !(d->ndim == 1 && d->radius <= 4))
         return fail(SB200_ERR_UNSUPPORTED, "LINE1D kernel needs ndim=1, radius 1..4");
     if (c.kernel == SB200_KERNEL_TMA3D && !tma3d_supports(d))
-        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3 and radius=1 (star or box) or radius=2 (star)");
+        return fail(SB200_ERR_UNSUPPORTED, "TMA3D kernel needs ndim=3 and radius=1 (star or box) or radius 2..4 (star)");
     if (c.kernel == SB200_KERNEL_RESIDENT2D &&
         !(d->ndim == 2 && d->radius == 1 && resident2d_fits((long long)d->n[0], (long long)d->n[1], (int)esize(d->dtype))))
         return fail(SB200_ERR_UNSUPPORTED, "RESIDENT2D kernel needs ndim=2, radius=1 and a grid that fits one "
@@ -484,7 +504,7 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             if (g.r > 1) {
-                if (k != 1) return fail(SB200_ERR_INVALID, "the radius-2 TMA3D kernel fuses 1 step");
+                if (k != 1) return fail(SB200_ERR_INVALID, "the radius-2..4 TMA3D kernel fuses 1 step");
                 return launch_tma3dr<T>(a, b, d->dtype, g, ob, oe, st, tile_pref(d));
             }
             return launch_tma3d<T>(a, b, d->dtype, g, t3_shape(d),
@@ -730,8 +750,8 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
         info->chunks = (uint32_t)p.nchunks;
         info->chunk_extent = (uint32_t)p.chunk_rows;
     } else if (c.kernel == SB200_KERNEL_TMA3D && desc->radius > 1) {
-        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan<double, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
-                                                  : t3r_plan<float, 2>(g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
+        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan_any<double>(g.r, g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
+                                                  : t3r_plan_any<float>(g.r, g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
         info->tiles_x = (uint32_t)p.ntx;
         info->tiles_y = (uint32_t)p.nty;
         info->chunks = (uint32_t)p.nchunks;
@@ -937,9 +957,9 @@ static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
         }
         return SB200_OK;
     }
-    if (g.r > 1) {  // 13-point star (tma3dr.cuh)
-        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan<double, 2>(g.n[0], g.n[1], 1, DS().sm_count)
-                                                  : t3r_plan<float, 2>(g.n[0], g.n[1], 1, DS().sm_count);
+    if (g.r > 1) {  // radius 2..4 star (tma3dr.cuh)
+        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan_any<double>(g.r, g.n[0], g.n[1], 1, DS().sm_count, 0)
+                                                  : t3r_plan_any<float>(g.r, g.n[0], g.n[1], 1, DS().sm_count, 0);
         if (arrivals) *arrivals = (uint32_t)(p.ntx * p.nty);
         if (desc->dtype == SB200_F64)
             return launch_tma3dr<double>((const double*)a, (double*)b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);

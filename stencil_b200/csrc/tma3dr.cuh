@@ -1,5 +1,5 @@
-// tma3dr.cuh — 3-D star stencil of radius 2 (13-point), one time step per launch, in the
-// tma3d framework (what the reference's `-r` flag asks of a 3-D grid: program_options.cpp:22-23;
+// tma3dr.cuh — 3-D star stencils of radius R = 2..4 (13-, 19-, 25-point), one time step per launch,
+// in the tma3d framework (what the reference's `-r` flag asks of a 3-D grid: program_options.cpp:22-23;
 // its general-radius tile kernel is neighbors_impl, stencil_dma.cpp:571-1099).
 //
 // Same machinery as tma3d.cuh: a CTA owns a 64(32*PXV) x 64 xy tile with an R-wide halo and
@@ -16,8 +16,9 @@
 // near->far (one add per later plane); one multiply by avg = 1/(6R).  Bit-identical.
 //
 // One step per launch (K = 1): 2R plane-sized arrays of state per level leave no room for a
-// second level at 512 threads x 128 registers.  The win over the one-thread-per-vector generic
-// kernel is the memory system (TMA tiles, z re-use in registers), not fusion.
+// second level at 512 threads x 128 registers — at R >= 3 not even for four rows per thread, so
+// those radii use 64 x 32 tiles (two rows per thread).  The win over the one-thread-per-vector
+// generic kernel is the memory system (TMA tiles, z re-use in registers), not fusion.
 #pragma once
 #include "tma3d.cuh"
 
@@ -25,7 +26,7 @@ namespace sb200 {
 
 template <class T, int R> struct T3R {
     static constexpr int PXV = 16 / (int)sizeof(T);
-    static constexpr int PY = 4;
+    static constexpr int PY = R == 2 ? 4 : 2;  // rows per thread: the register budget (2R state arrays)
     static constexpr int TXN = 32, TYN = 16;
     static constexpr int THREADS = TXN * TYN;
     static constexpr int BX = TXN * PXV, BY = TYN * PY;
@@ -61,7 +62,7 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
                     T avg, const SlabLinkDev link) {
     using C = T3R<T, R>;
     constexpr int PXV = C::PXV, PY = C::PY, S = C::STAGES;
-    static_assert(R == 2, "only the 13-point star is instantiated");
+    static_assert(R >= 2 && R <= 4, "radius 2..4");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned char* base = smem_raw + ((128 - (smem_u32(smem_raw) & 127)) & 127);
     T* ring = reinterpret_cast<T*>(base);
@@ -211,11 +212,17 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
             }
         }
     };
+    // the plane loop is unrolled by R so that the phase (plane mod R) is a compile-time constant;
+    // steps past nin wait for nothing and store nothing
+    auto steps_R = [&](auto self, auto Pc, int j) {
+        constexpr int P = decltype(Pc)::value;
+        if constexpr (P < R) {
+            step(IC<P>{}, j + P);
+            self(self, IC<P + 1>{}, j);
+        }
+    };
 #pragma unroll 1
-    for (int j = 0; j < nin; j += R) {
-        step(IC<0>{}, j);
-        if constexpr (R > 1) step(IC<1 % R>{}, j + 1);
-    }
+    for (int j = 0; j < nin; j += R) steps_R(steps_R, IC<0>{}, j);
     if (tid == 0) tma_store_wait_all();
     if (LINKED && (is_lo || is_hi)) {
         // face push (as in tma3d.cuh): this CTA's TMA stores are complete (thread 0 waited, then

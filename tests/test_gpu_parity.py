@@ -182,11 +182,13 @@ def test_tma3d_box27_kernel(gpu, n, T, k, dtype):
     ((1, 1, 1), 3), ((5, 4, 3), 4), ((60, 60, 20), 3), ((61, 59, 33), 5), ((130, 70, 40), 2),
     ((200, 130, 17), 3), ((123, 125, 64), 4), ((300, 64, 9), 2), ((57, 121, 5), 1),
 ])
-def test_tma3d_radius2_star_kernel(gpu, n, T, dtype):
-    """13-point star (3-D radius 2) through the TMA kernel (z history in registers), bit-exact."""
-    t = _check(n, 2, capi.STAR, dtype, T, kernel=capi.KERNEL_TMA3D)
+@pytest.mark.parametrize("r", [2, 3, 4])
+def test_tma3d_radius2_star_kernel(gpu, n, T, r, dtype):
+    """13- / 19- / 25-point star (3-D radius 2..4) through the TMA kernel (z history in registers),
+    bit-exact."""
+    t = _check(n, r, capi.STAR, dtype, T, kernel=capi.KERNEL_TMA3D)
     assert t.kernel == capi.KERNEL_TMA3D and t.time_block == 1 and t.launches == T
-    assert _check(n, 2, capi.STAR, dtype, T).kernel == capi.KERNEL_TMA3D   # AUTO picks it
+    assert _check(n, r, capi.STAR, dtype, T).kernel == capi.KERNEL_TMA3D   # AUTO picks it
 
 
 @pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
@@ -222,7 +224,8 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70, 20), 2, capi.STAR, np.float64, 2).kernel == capi.KERNEL_TMA3D
-    assert _check((80, 70, 20), 3, capi.STAR, np.float64, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70, 20), 3, capi.STAR, np.float64, 2).kernel == capi.KERNEL_TMA3D
+    assert _check((80, 70, 20), 5, capi.STAR, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 3, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
@@ -307,7 +310,7 @@ def test_resident2d_auto_and_limits(gpu):
     ((70, 66, 12), 1, 4, 2), ((130, 61, 9), 1, 5, 2), ((64, 64, 40), 1, 3, 1),            # 3-D: TMA3D, faces are planes
     ((300, 40), 1, 9, 4), ((131, 24), 1, 7, 2), ((700, 300), 1, 13, 6), ((64, 17), 1, 5, 1),  # 2-D: WARP2D, faces are rows
     ((300, 64), 2, 7, 2), ((131, 40), 2, 5, 1), ((260, 90), 3, 5, 2), ((200, 70), 4, 3, 1),   # 2-D radius > 1 (warp2dr)
-    ((70, 66, 16), 2, 4, 1), ((130, 61, 11), 2, 3, 1),                                        # 3-D 13-point (tma3dr)
+    ((70, 66, 16), 2, 4, 1), ((130, 61, 11), 2, 3, 1), ((70, 66, 18), 3, 3, 1), ((90, 61, 16), 4, 2, 1),  # 3-D radius 2..4 (tma3dr)
 ])
 def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     """The fused halo exchange (sb200_sweep_slab_linked: peer stores + arrival counters) on
@@ -315,7 +318,7 @@ def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     axis.  For T <= n_outer that equals the middle copy of three stacked copies swept with the
     ordinary Dirichlet oracle, bit for bit."""
     import torch
-    if shape == capi.BOX and (r > 2 or (r == 2 and len(n) == 3)):
+    if shape == capi.BOX and (r > 2 or (r >= 2 and len(n) == 3)):
         pytest.skip("no fused box kernel at this radius")
     d = capi.make_desc(n, r, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
     k = min(k, int(capi.lib().sb200_max_time_block(ctypes.byref(d))))

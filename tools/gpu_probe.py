@@ -72,10 +72,11 @@ if "rad" in which:  # general-radius 2-D star: fused warp kernel vs the one-thre
                         capi.make_desc((8192, 8192), r, capi.STAR, dt, 24, kernel=capi.KERNEL_WARP2D))):
                     run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 24, capi.KERNEL_WARP2D, k, r=r)
             run(f"r{r}-{nm}", (8192, 8192), capi.STAR, dt, 8, capi.KERNEL_GENERIC, 1, r=r)
-if "star13" in which:  # 3-D radius-2 star: TMA kernel vs one-thread-per-vector kernel
+if "star13" in which:  # 3-D radius 2..4 star: TMA kernel vs one-thread-per-vector kernel
     for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
-        run(f"star13-{nm}", (512, 512, 512), capi.STAR, dt, 12, capi.KERNEL_TMA3D, 1, r=2)
-        run(f"star13-{nm}", (512, 512, 512), capi.STAR, dt, 6, capi.KERNEL_GENERIC, 1, r=2)
+        for r in (2, 3, 4):
+            run(f"star3d-r{r}-{nm}", (512, 512, 512), capi.STAR, dt, 12, capi.KERNEL_TMA3D, 1, r=r)
+            run(f"star3d-r{r}-{nm}", (512, 512, 512), capi.STAR, dt, 6, capi.KERNEL_GENERIC, 1, r=r)
 if "box2" in which:  # 25-point box: fused warp kernel vs one launch per step
     for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
         for k in (1, 2):
