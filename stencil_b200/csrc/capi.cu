@@ -439,11 +439,16 @@ bool warp2d_supports(const sb200_desc* d) {
 bool tma3d_supports(const sb200_desc* d) {
     return d->ndim == 3 && (d->radius == 1 || (d->radius >= 2 && d->radius <= 4 && d->shape == SB200_STAR));
 }
+// What AUTO takes from it: at radius 3 and 4 the two-rows-per-thread tiles pay off in fp64 only
+// (1.37-1.40x the generic kernel; fp32 1.03x / 0.96x: profiles/r02o_star3d_probe.log).
+bool tma3d_preferred(const sb200_desc* d) {
+    return tma3d_supports(d) && (d->radius <= 2 || d->dtype == SB200_F64);
+}
 
 Choice choose(const sb200_desc* d) {
     Choice c;
     const bool w2d_ok = warp2d_supports(d);
-    const bool t3_ok = tma3d_supports(d);
+    const bool t3_ok = tma3d_preferred(d);
     const bool l1_ok = d->ndim == 1 && d->radius <= 4;
     int kern = d->kernel;
     if (kern == SB200_KERNEL_AUTO)

@@ -188,7 +188,9 @@ def test_tma3d_radius2_star_kernel(gpu, n, T, r, dtype):
     bit-exact."""
     t = _check(n, r, capi.STAR, dtype, T, kernel=capi.KERNEL_TMA3D)
     assert t.kernel == capi.KERNEL_TMA3D and t.time_block == 1 and t.launches == T
-    assert _check(n, r, capi.STAR, dtype, T).kernel == capi.KERNEL_TMA3D   # AUTO picks it
+    # AUTO picks it at radius 2, and at radius 3..4 in fp64 (where it beats the generic kernel)
+    auto = capi.KERNEL_TMA3D if (r == 2 or dtype == np.float64) else capi.KERNEL_GENERIC
+    assert _check(n, r, capi.STAR, dtype, T).kernel == auto
 
 
 @pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
@@ -320,6 +322,8 @@ def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     import torch
     if shape == capi.BOX and (r > 2 or (r >= 2 and len(n) == 3)):
         pytest.skip("no fused box kernel at this radius")
+    if len(n) == 3 and r >= 3 and dtype == np.float32:
+        pytest.skip("AUTO keeps the generic kernel for 3-D radius 3..4 in fp32")
     d = capi.make_desc(n, r, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
     k = min(k, int(capi.lib().sb200_max_time_block(ctypes.byref(d))))
     no = n[-1]
