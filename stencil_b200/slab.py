@@ -9,7 +9,7 @@ internal face, exchanged once per fused block of k time steps:
     per block; its face CTAs (warps in 2-D) run first and store their planes straight into the neighbours' ghost planes over
     NVLink (CUDA IPC peer mappings), signalling arrival counters the neighbours' next launch
     acquires — no NCCL call, no extra launch, no host sync on the data path
-    (csrc/tma3d.cuh: SlabLinkDev).
+    (csrc/slablink.cuh: SlabLinkDev).
   exchange="nccl" (radius > 1, generic kernel, and the measured baseline):
     faces first (side stream)  ->  send/recv face planes (NCCL, NVLink)   \
     interior planes (main stream, concurrently)                             -> join
