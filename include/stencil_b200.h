@@ -76,9 +76,11 @@ typedef struct sb200_desc {
 
 typedef enum sb200_flags {
     SB200_FLAG_NONE = 0,
-    /* Allow kernels that re-associate the sum of a point (separable box sums): results
-     * then agree with the reference order within the north-star tolerance (max relative
-     * error 1e-12 fp64 / 1e-5 fp32) instead of bit for bit.  Off by default. */
+    /* Allow kernels that re-associate the sum of a point (separable box sums: the 27-point
+     * TMA3D kernel and the 9-point WARP2D kernel have such a level): results then agree
+     * with the reference order within the north-star tolerance (max relative error 1e-12
+     * fp64 / 1e-5 fp32) instead of bit for bit.  Off by default; shapes without a
+     * separable level (stars, radius > 1) stay bit-exact under it. */
     SB200_FLAG_REASSOCIATE = 1,
     /* Read block_hint (the reference's -b/--block-size: the side of the tile one CPE owns) as
      * this backend's tile preference: the number of rows (2-D) / planes (3-D) of the outermost

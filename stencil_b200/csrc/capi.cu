@@ -26,7 +26,8 @@
 #include "tma3d.cuh"
 #include "tma3dr.cuh"
 #include "util_kernels.cuh"
-#include "warp2d.cuh"
+#include "warp2d_api.h"
+#include "warp2d.cuh"   // planner and limits only: the kernels are instantiated in warp2d.cu
 #include "warp2dr.cuh"
 #include "line1d.cuh"
 
@@ -445,6 +446,12 @@ bool tma3d_preferred(const sb200_desc* d) {
     return tma3d_supports(d) && (d->radius <= 2 || d->dtype == SB200_F64);
 }
 
+// Kernel shape of the tma3d family and of the radius-1 warp2d kernel: the separable box under
+// SB200_FLAG_REASSOCIATE.
+int t3_shape(const sb200_desc* d) {
+    return d->shape == SB200_BOX && (d->flags & SB200_FLAG_REASSOCIATE) ? (int)BOXSEP : d->shape;
+}
+
 Choice choose(const sb200_desc* d) {
     Choice c;
     const bool w2d_ok = warp2d_supports(d);
@@ -462,7 +469,8 @@ Choice choose(const sb200_desc* d) {
               : kern == SB200_KERNEL_LINE1D ? L1D_MAXK : 1;
     int k = (int)d->time_block;
     if (kern == SB200_KERNEL_RESIDENT2D) k = c.max_k;  // the whole call is one launch
-    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? c.max_k : 4) : kern == SB200_KERNEL_LINE1D ? l1d_default_k((int)d->radius) : kern == SB200_KERNEL_TMA3D ? 2 : 1;
+    // radius-1 warp kernel: 4 fused steps (the separable box of SB200_FLAG_REASSOCIATE is cheap enough for 6)
+    if (k == 0) k = kern == SB200_KERNEL_WARP2D ? (d->radius > 1 ? c.max_k : t3_shape(d) == BOXSEP ? 6 : 4) : kern == SB200_KERNEL_LINE1D ? l1d_default_k((int)d->radius) : kern == SB200_KERNEL_TMA3D ? 2 : 1;
     if (k > c.max_k) k = c.max_k;
     c.k = k;
     return c;
@@ -482,11 +490,6 @@ int check_choice(const sb200_desc* d, const Choice& c) {
     return SB200_OK;
 }
 
-// Kernel shape of the tma3d family: the separable box under SB200_FLAG_REASSOCIATE.
-int t3_shape(const sb200_desc* d) {
-    return d->shape == SB200_BOX && (d->flags & SB200_FLAG_REASSOCIATE) ? (int)BOXSEP : d->shape;
-}
-
 // -b/--block-size as a tile preference (opt-in): rows / planes one CTA or warp streams.
 int tile_pref(const sb200_desc* d) {
     return (d->flags & SB200_FLAG_BLOCK_TILE) && d->block_hint > 0 ? (int)(d->block_hint > (1u << 20) ? (1u << 20) : d->block_hint) : 0;
@@ -503,9 +506,9 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_WARP2D:
             if (g.r > 1)
-                CU_TRY(launch_warp2dr<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
+                CU_TRY(launch_warp2dr_any(a, b, (int)sizeof(T), g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st, nullptr));
             else
-                CU_TRY(launch_warp2d<T>(a, b, g, d->shape, dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st));
+                CU_TRY(launch_warp2d_any(a, b, (int)sizeof(T), g, t3_shape(d), dom, k, ob, oe, Tuning{DS().sm_count, tile_pref(d)}, st, nullptr));
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             if (g.r > 1) {
@@ -950,16 +953,10 @@ static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
         // face owners are warps: one per x strip and face
         if (arrivals) *arrivals = (uint32_t)w2d_plan(g.n[0], n, (int)steps, DS().sm_count, g.r, 0).nstrips;
         const Tuning tn{DS().sm_count, tile_pref(desc)};
-        if (g.r > 1) {
-            if (desc->dtype == SB200_F64)
-                CU_TRY(launch_warp2dr<double>((const double*)a, (double*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
-            else
-                CU_TRY(launch_warp2dr<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
-        } else if (desc->dtype == SB200_F64) {
-            CU_TRY(launch_warp2d<double>((const double*)a, (double*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
-        } else {
-            CU_TRY(launch_warp2d<float>((const float*)a, (float*)b, g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
-        }
+        if (g.r > 1)
+            CU_TRY(launch_warp2dr_any(a, b, (int)esize(desc->dtype), g, desc->shape, dom, (int)steps, ob, oe, tn, st, &L));
+        else
+            CU_TRY(launch_warp2d_any(a, b, (int)esize(desc->dtype), g, t3_shape(desc), dom, (int)steps, ob, oe, tn, st, &L));
         return SB200_OK;
     }
     if (g.r > 1) {  // radius 2..4 star (tma3dr.cuh)

@@ -49,7 +49,7 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // Bounded acquire-spin on an arrival counter: gives up after 10 s, and at once if another
 // CTA already gave up — a broken link ends in a reported error (sb200_link_status), never
 // in a hung GPU.
-__device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsigned* err_flag) {
+static __device__ __noinline__ void link_wait(const unsigned* flag, unsigned want, unsigned* err_flag) {
     const unsigned long long t0 = global_timer_ns();
     while ((int)(ld_acquire_sys_u32(flag) - want) < 0) {
         if (global_timer_ns() - t0 > 10000000000ull || *(volatile unsigned*)err_flag != 0u) {

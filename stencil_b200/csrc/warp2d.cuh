@@ -124,6 +124,34 @@ template <class T> struct W2dLevel<T, BOX> {
     }
 };
 
+// 9-point box with separable sums (SB200_FLAG_REASSOCIATE): row sum rs = (xl + c) + xr, output row
+// y-1 = ((rs(y-2) + rs(y-1)) + rs(y)) * avg — 4 adds + 1 multiply per point and level instead of
+// 9 + 1, in an order the reference does not use: equal within 1e-5 (fp32) / 1e-12 (fp64) relative.
+template <class T> struct W2dLevel<T, BOXSEP> {
+    T p2[4];   // row sum of row y-2
+    T p1[4];   // row sum of row y-1
+    T cm1[4];  // previous row, pass-through value
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p2[i] = p1[i] = cm1[i] = T(0);
+    }
+    template <bool EDGE>
+    __device__ __forceinline__ void step(const Row4<T>& c, T l, T rg, T avg, unsigned upd,
+                                         Row4<T>& o) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const T xl = i == 0 ? l : c.v[i - 1];
+            const T xr = i == 3 ? rg : c.v[i + 1];
+            const T rs = add_rn(add_rn(xl, c.v[i]), xr);
+            const T f = mul_rn(add_rn(add_rn(p2[i], p1[i]), rs), avg);
+            o.v[i] = (!EDGE || ((upd >> i) & 1u)) ? f : cm1[i];
+            p2[i] = p1[i];
+            p1[i] = rs;
+            if (EDGE) cm1[i] = c.v[i];
+        }
+    }
+};
+
 template <class T>
 __device__ __forceinline__ T shfl_up1(T v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 template <class T>
@@ -359,7 +387,7 @@ static cudaError_t launch_warp2d_k(const T* in, T* out, const Grid& g, Domain do
                                    long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link_in) {
     if (oe <= ob) return cudaSuccess;
     const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, 1, tn.prefer_chunk);
-    const T avg = Avg<T>::value(SHAPE, 2, 1);
+    const T avg = Avg<T>::value(SHAPE == BOXSEP ? (int)BOX : SHAPE, 2, 1);
     if (link_in && (link_in->link_lo || link_in->link_hi)) {
         SlabLinkDev link = *link_in;
         long long nc = p.nchunks;
@@ -395,8 +423,9 @@ template <class T>
 static cudaError_t launch_warp2d(const T* in, T* out, const Grid& g, int shape, Domain dom, int K,
                                  long long ob, long long oe, const Tuning& tn, cudaStream_t st,
                                  const SlabLinkDev* link = nullptr) {
-    return shape == STAR ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, tn, st, link)
-                         : launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, tn, st, link);
+    return shape == STAR  ? launch_warp2d_s<T, STAR>(in, out, g, dom, K, ob, oe, tn, st, link)
+           : shape == BOX ? launch_warp2d_s<T, BOX>(in, out, g, dom, K, ob, oe, tn, st, link)
+                          : launch_warp2d_s<T, BOXSEP>(in, out, g, dom, K, ob, oe, tn, st, link);
 }
 
 }  // namespace sb200

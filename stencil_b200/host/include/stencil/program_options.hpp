@@ -41,6 +41,7 @@ struct ProgramOptions {
     std::string kernel = "auto";  // auto | generic | warp2d | tma3d | resident2d
     unsigned gpus = 1;            // GPUs one CUDA run is spread over (slabs of the outermost axis)
     bool resident = false;        // CUDA: device-resident run over the GPU group (no host grids; RMA-style)
+    bool reassociate = false;     // allow separable box sums (SB200_FLAG_REASSOCIATE): -c then passes by tolerance
     bool block_as_tile = false;   // read -b as the CUDA tile preference (rows / planes per warp / CTA)
     std::string json_path;        // append one JSON record per method here
     std::string bmp_path;         // write the final 2-D field as a BMP heat map

@@ -105,7 +105,7 @@ sb200_desc make_desc(ProgramOptions const& o) {
     d.time_block = o.time_block;
     d.block_hint = o.block_size;
     d.ngpus = o.gpus;
-    d.flags = o.block_as_tile ? SB200_FLAG_BLOCK_TILE : SB200_FLAG_NONE;
+    d.flags = (o.block_as_tile ? SB200_FLAG_BLOCK_TILE : SB200_FLAG_NONE) | (o.reassociate ? SB200_FLAG_REASSOCIATE : SB200_FLAG_NONE);
     d.kernel = o.kernel == "generic" ? SB200_KERNEL_GENERIC
                : o.kernel == "warp2d" ? SB200_KERNEL_WARP2D
                : o.kernel == "tma3d"  ? SB200_KERNEL_TMA3D

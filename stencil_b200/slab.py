@@ -37,6 +37,7 @@ def resolve_kernel(desc: capi.Desc):
     t3 = desc.ndim == 3 and (desc.radius == 1 or (desc.shape == capi.STAR and (
         desc.radius == 2 or (3 <= desc.radius <= 4 and desc.dtype == capi.F64))))
     l1 = desc.ndim == 1 and desc.radius <= 4
+    sep9 = desc.shape == capi.BOX and bool(desc.flags & capi.FLAG_REASSOCIATE)     # separable 9-point box
     kern = desc.kernel
     if kern == capi.KERNEL_AUTO:
         kern = (capi.KERNEL_WARP2D if w2d else capi.KERNEL_TMA3D if t3
@@ -47,7 +48,7 @@ def resolve_kernel(desc: capi.Desc):
     if max_k < 1:
         raise capi.StencilError(max_k, capi.lib().sb200_last_error().decode())
     k = desc.time_block or {capi.KERNEL_GENERIC: 1, capi.KERNEL_TMA3D: 2, capi.KERNEL_LINE1D: min(16, 32 // max(1, desc.radius)),
-                            capi.KERNEL_WARP2D: 4 if desc.radius == 1 else max_k}[kern]
+                            capi.KERNEL_WARP2D: (6 if sep9 else 4) if desc.radius == 1 else max_k}[kern]
     return kern, min(k, max_k)
 
 

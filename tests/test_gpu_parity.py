@@ -21,11 +21,11 @@ def _oracle_pair(n, r, dtype, seed):
     return oracle.fill(n, r, code, init, seed), oracle.fill(n, r, code, oracle.INIT_REF)
 
 
-def _check(n, r, shape, dtype, T, seed=1, time_block=0, kernel=capi.KERNEL_AUTO):
+def _check(n, r, shape, dtype, T, seed=1, time_block=0, kernel=capi.KERNEL_AUTO, flags=0):
     a, b = _oracle_pair(n, r, dtype, seed)
     ga, gb = a.copy(), b.copy()
     want = b if oracle.sweep(n, r, shape, T, a, b, threads=oracle.max_threads()) else a
-    got, t = sweep.run_host(n, ga, gb, T, radius=r, shape=shape, time_block=time_block, kernel=kernel)
+    got, t = sweep.run_host(n, ga, gb, T, radius=r, shape=shape, time_block=time_block, kernel=kernel, flags=flags)
     assert t.result_in_out == (T & 1)
     assert got is (gb if T & 1 else ga)
     assert np.array_equal(want.view(np.uint8), got.view(np.uint8)), \
@@ -217,6 +217,33 @@ def test_tma3d_box27_reassociated_within_tolerance(gpu, n, T, k, seed, dtype, to
     # without the flag the same call is bit-exact
     ga2, gb2 = _oracle_pair(n, 1, dtype, seed)
     got2, _ = sweep.run_host(n, ga2, gb2, T, radius=1, shape=capi.BOX, time_block=k, kernel=capi.KERNEL_TMA3D)
+    assert np.array_equal(want.view(np.uint8), got2.view(np.uint8))
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
+@pytest.mark.parametrize("n,T,k,seed", [
+    ((1, 1), 3, 2, 1), ((5, 4), 3, 1, 1), ((131, 77), 7, 3, 1), ((300, 200), 12, 4, 2), ((97, 403), 30, 6, 3),
+    ((1000, 300), 60, 4, 1), ((260, 240), 24, 6, 0),
+])
+def test_warp2d_box9_reassociated_within_tolerance(gpu, n, T, k, seed, dtype, tol):
+    """SB200_FLAG_REASSOCIATE in 2-D: the separable 9-point level (row sums kept across rows) against
+    the reference-order oracle, same bar as the 27-point test above; without the flag bit-exact."""
+    a, b = _oracle_pair(n, 1, dtype, seed)
+    ga, gb = a.copy(), b.copy()
+    want = b if oracle.sweep(n, 1, capi.BOX, T, a, b, threads=oracle.max_threads()) else a
+    got, t = sweep.run_host(n, ga, gb, T, radius=1, shape=capi.BOX, time_block=k, flags=capi.FLAG_REASSOCIATE)
+    assert t.kernel == capi.KERNEL_WARP2D
+    w, g = want.astype(np.float64), got.astype(np.float64)
+    assert np.array_equal(w == 0, g == 0), "zero sets differ"
+    scale = np.maximum(np.abs(w), np.abs(g))
+    rel = np.abs(w - g)[scale > 0] / scale[scale > 0]
+    assert rel.size == 0 or rel.max() <= tol, f"max relative error {rel.max():.3e}"
+    if n[0] > 100:
+        assert not np.array_equal(want.view(np.uint8), got.view(np.uint8)), "the flag changed nothing: separable level not used?"
+    # the star has no separable form: the flag leaves it bit-exact
+    _check(n, 1, capi.STAR, dtype, T, seed=seed, time_block=k, flags=capi.FLAG_REASSOCIATE)
+    ga2, gb2 = _oracle_pair(n, 1, dtype, seed)
+    got2, _ = sweep.run_host(n, ga2, gb2, T, radius=1, shape=capi.BOX, time_block=k)
     assert np.array_equal(want.view(np.uint8), got2.view(np.uint8))
 
 

@@ -89,3 +89,22 @@ def test_cuda_method_self_check(gpu, extra):
     assert "The results of method CUDA is correct." in r.stdout
     assert "bit-exact vs naive loop: yes" in r.stdout
     assert re.search(AVG, r.stdout)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("extra", [
+    ["-s", 700, "-i", 24, "-b", 1, "--stencil", "box", "--init", "random"],                                   # 9-point, fp32
+    ["-s", 1, "-i", 8, "-b", 1, "--shape", "130,120,70", "--stencil", "box", "--dtype", "f64", "--init", "random"],  # 27-point
+])
+def test_cuda_reassociate_passes_the_reference_check_by_tolerance(gpu, extra):
+    """--reassociate (SB200_FLAG_REASSOCIATE): the reference's own -c check is a tolerance check
+    (stencil.cpp:75-151, 1e-4 absolute), which the separable sums pass without being bit-exact."""
+    r = run(*extra, "-m", "CUDA", "-c", "--reassociate")
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "The results of method CUDA is correct." in r.stdout
+    assert "bit-exact vs naive loop: no" in r.stdout
+
+
+def test_reassociate_with_resident_check_is_refused(built):
+    r = run("-s", 64, "-i", 2, "-b", 1, "-m", "CUDA", "-c", "--resident", "--reassociate")
+    assert r.returncode != 0 and "naive order" in (r.stdout + r.stderr)

@@ -14,8 +14,8 @@ capi.check(capi.lib().sb200_init(0))
 PEAK = 6529.1
 
 
-def run(name, n, shape, dtype, T, kernel, k, reps=3, r=1):
-    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel)
+def run(name, n, shape, dtype, T, kernel, k, reps=3, r=1, flags=0):
+    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel, flags=flags)
     try:
         g = sweep.DeviceGrids(d)
         g.fill(capi.INIT_RANDOM, seed=1)
@@ -59,6 +59,11 @@ if "c4" in which:
     for k in (1, 2, 4, 6):
         run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k)
     run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 6, capi.KERNEL_GENERIC, 1)
+if "sep9" in which:  # separable 9-point box (SB200_FLAG_REASSOCIATE) against the reference-order level
+    for dt, nm, n in ((capi.F32, "f32", 16384), (capi.F64, "f64", 8192)):
+        for k in (2, 4, 6):
+            run(f"9pt-{nm}", (n, n), capi.BOX, dt, 48, capi.KERNEL_WARP2D, k)
+            run(f"9pt-{nm}-sep", (n, n), capi.BOX, dt, 48, capi.KERNEL_WARP2D, k, flags=capi.FLAG_REASSOCIATE)
 if "c3" in which:
     run("c3-27pt", (512, 512, 512), capi.BOX, capi.F64, 6, capi.KERNEL_GENERIC, 1)
     for k in (1, 2):
