@@ -25,6 +25,7 @@
 #include "resident2d_api.h"
 #include "tma3d.cuh"
 #include "tma3dr.cuh"
+#include "tma3db_api.h"
 #include "util_kernels.cuh"
 #include "warp2d_api.h"
 #include "warp2d.cuh"   // planner and limits only: the kernels are instantiated in warp2d.cu
@@ -415,7 +416,27 @@ int launch_tma3dr(const T* in, T* out, int dtype, const Grid& g, long long ob, l
     return fail(SB200_ERR_INVALID, "TMA3D star kernel: radius %d out of range", g.r);
 }
 
-// tiles / chunks of the radius-R star kernel (host logic)
+// 3-D box of radius 2 (125-point), one step per launch (tma3db.cuh, instantiated in tma3db.cu).
+int launch_tma3db(const void* in, void* out, int dtype, const Grid& g, long long ob, long long oe, cudaStream_t st,
+                  int prefer_chunk, const SlabLinkDev* link = nullptr) {
+    if (oe <= ob) return SB200_OK;
+    if (g.r != 2) return fail(SB200_ERR_INVALID, "TMA3D box kernel: radius %d out of range", g.r);
+    const int es = (int)esize(dtype);
+    int bx, by, vx, vy;
+    tma3db_tile(es, g.n[0], &bx, &by, &vx, &vy);
+    const CUtensorMap* mp = nullptr;
+    if (int rc = get_tensor_map(in, dtype, g, bx, by, false, &mp)) return rc;
+    const CUtensorMap imap = *mp;
+    if (int rc = get_tensor_map(out, dtype, g, vx, vy, true, &mp)) return rc;
+    const CUtensorMap omap = *mp;
+    const T3Plan p = tma3db_plan(es, g.n[0], g.n[1], oe - ob, DS().sm_count, prefer_chunk);
+    CU_TRY(launch_tma3db_any(imap, omap, out, es, g, ob, oe, p, st, link));
+    return SB200_OK;
+}
+
+// tiles / chunks of the radius-R star / radius-2 box kernels (host logic)
+T3Plan t3rb_plan(const sb200_desc* d, const Grid& g, long long planes, int sm_count, int prefer);
+
 template <class T>
 T3Plan t3r_plan_any(int r, long long nx, long long ny, long long planes, int sm_count, int prefer) {
     return r == 2 ? t3r_plan<T, 2>(nx, ny, planes, sm_count, prefer)
@@ -436,9 +457,15 @@ bool warp2d_supports(const sb200_desc* d) {
                             (d->shape == SB200_BOX && d->radius == 2));
 }
 
-// TMA3D family: radius 1 star / box (tma3d.cuh), radius 2..4 star (tma3dr.cuh).
+// TMA3D family: radius 1 star / box (tma3d.cuh), radius 2..4 star (tma3dr.cuh), radius 2 box (tma3db.cuh).
 bool tma3d_supports(const sb200_desc* d) {
-    return d->ndim == 3 && (d->radius == 1 || (d->radius >= 2 && d->radius <= 4 && d->shape == SB200_STAR));
+    return d->ndim == 3 && (d->radius == 1 || (d->radius >= 2 && d->radius <= 4 && d->shape == SB200_STAR) ||
+                            (d->radius == 2 && d->shape == SB200_BOX));
+}
+T3Plan t3rb_plan(const sb200_desc* d, const Grid& g, long long planes, int sm_count, int prefer) {
+    if (d->shape == SB200_BOX) return tma3db_plan((int)esize(d->dtype), g.n[0], g.n[1], planes, sm_count, prefer);
+    return d->dtype == SB200_F64 ? t3r_plan_any<double>(g.r, g.n[0], g.n[1], planes, sm_count, prefer)
+                                 : t3r_plan_any<float>(g.r, g.n[0], g.n[1], planes, sm_count, prefer);
 }
 // What AUTO takes from it: at radius 3 and 4 the two-rows-per-thread tiles pay off in fp64 only
 // (1.37-1.40x the generic kernel; fp32 1.03x / 0.96x: profiles/r02o_star3d_probe.log).
@@ -512,7 +539,8 @@ int pass_t(const sb200_desc* d, const Choice& c, const Grid& g, Domain dom, cons
             return SB200_OK;
         case SB200_KERNEL_TMA3D:
             if (g.r > 1) {
-                if (k != 1) return fail(SB200_ERR_INVALID, "the radius-2..4 TMA3D kernel fuses 1 step");
+                if (k != 1) return fail(SB200_ERR_INVALID, "the radius-2..4 TMA3D kernels fuse 1 step");
+                if (d->shape == SB200_BOX) return launch_tma3db(a, b, d->dtype, g, ob, oe, st, tile_pref(d));
                 return launch_tma3dr<T>(a, b, d->dtype, g, ob, oe, st, tile_pref(d));
             }
             return launch_tma3d<T>(a, b, d->dtype, g, t3_shape(d),
@@ -758,8 +786,7 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
         info->chunks = (uint32_t)p.nchunks;
         info->chunk_extent = (uint32_t)p.chunk_rows;
     } else if (c.kernel == SB200_KERNEL_TMA3D && desc->radius > 1) {
-        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan_any<double>(g.r, g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc))
-                                                  : t3r_plan_any<float>(g.r, g.n[0], g.n[1], g.n[2], sm_count, tile_pref(desc));
+        const T3Plan p = t3rb_plan(desc, g, g.n[2], sm_count, tile_pref(desc));
         info->tiles_x = (uint32_t)p.ntx;
         info->tiles_y = (uint32_t)p.nty;
         info->chunks = (uint32_t)p.nchunks;
@@ -959,10 +986,10 @@ static int slab_linked_impl(const sb200_desc* desc, uint32_t ghost, int lo_is_bo
             CU_TRY(launch_warp2d_any(a, b, (int)esize(desc->dtype), g, t3_shape(desc), dom, (int)steps, ob, oe, tn, st, &L));
         return SB200_OK;
     }
-    if (g.r > 1) {  // radius 2..4 star (tma3dr.cuh)
-        const T3Plan p = desc->dtype == SB200_F64 ? t3r_plan_any<double>(g.r, g.n[0], g.n[1], 1, DS().sm_count, 0)
-                                                  : t3r_plan_any<float>(g.r, g.n[0], g.n[1], 1, DS().sm_count, 0);
+    if (g.r > 1) {  // radius 2..4 star (tma3dr.cuh), radius 2 box (tma3db.cuh)
+        const T3Plan p = t3rb_plan(desc, g, 1, DS().sm_count, 0);
         if (arrivals) *arrivals = (uint32_t)(p.ntx * p.nty);
+        if (desc->shape == SB200_BOX) return launch_tma3db(a, b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);
         if (desc->dtype == SB200_F64)
             return launch_tma3dr<double>((const double*)a, (double*)b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);
         return launch_tma3dr<float>((const float*)a, (float*)b, desc->dtype, g, ob, oe, st, tile_pref(desc), &L);

@@ -52,6 +52,52 @@ __device__ __forceinline__ T t3r_at(const T (&v)[PXV]) {
     else return __shfl_down_sync(0xffffffffu, v[EL], LANE);
 }
 
+// Face push of a LINKED launch (as in tma3d.cuh), shared by the radius-R star and box kernels:
+// this CTA's TMA stores are complete (thread 0 waited; then the barrier and the proxy fence);
+// every thread copies its part (PY rows of PXV points at gx, gy; s_rows = the rows it stores) of
+// the face planes into the neighbour's ghost planes, then thread 0 publishes them and counts
+// the CTA in.
+template <class T, int PXV, int PY>
+__device__ __forceinline__ void t3r_push_faces(T* __restrict__ out, const Grid& g, const SlabLinkDev& link, bool is_lo,
+                                               bool is_hi, long long gx, long long gy, unsigned s_rows, bool leader) {
+    __syncthreads();
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+    const long long plane_stride = g.pitch_x * g.pitch_y;
+    T* home = out + g.idx(gx, gy, 0);
+    const bool col_in = gx < g.n[0], col_full = gx + PXV <= g.n[0];
+#pragma unroll 1
+    for (int side = 0; side < 2; ++side) {
+        if (side == 0 ? !is_lo : !is_hi) continue;
+        const long long z0 = side == 0 ? 0 : g.n[2] - link.face_planes;
+        const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
+                                 (side == 0 ? link.shift_lo : link.shift_hi);
+#pragma unroll 1
+        for (int p = 0; p < link.face_planes; ++p) {
+            T* src = home + (z0 + p) * plane_stride;
+#pragma unroll
+            for (int i = 0; i < PY; ++i) {
+                if ((s_rows & (1u << i)) && col_in && gy + i < g.n[1]) {
+                    if (col_full) {
+                        T v[PXV];
+                        VecN<T, PXV>::ldcg(src + i * g.pitch_x, v);
+                        VecN<T, PXV>::st(src + rdelta + i * g.pitch_x, v);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < PXV; ++k)
+                            if (gx + k < g.n[0]) src[rdelta + i * g.pitch_x + k] = __ldcg(src + i * g.pitch_x + k);
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (leader) {
+        __threadfence_system();
+        if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
+        if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
+    }
+}
+
 // LINKED: the slab link of tma3d.cuh / slablink.cuh (faces are g = R planes; the CTAs of the first
 // / last z chunk own them, are dispatched first, acquire the neighbours' arrival counter before
 // their first TMA load and push their face planes after the z stream).
@@ -224,47 +270,8 @@ sweep_tma3dr_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
 #pragma unroll 1
     for (int j = 0; j < nin; j += R) steps_R(steps_R, IC<0>{}, j);
     if (tid == 0) tma_store_wait_all();
-    if (LINKED && (is_lo || is_hi)) {
-        // face push (as in tma3d.cuh): this CTA's TMA stores are complete (thread 0 waited, then
-        // the barrier and the proxy fence); every thread copies its part of the face planes into
-        // the neighbour's ghost planes, then thread 0 publishes them and counts the CTA in
-        __syncthreads();
-        asm volatile("fence.proxy.async.global;" ::: "memory");
-        const long long plane_stride = g.pitch_x * g.pitch_y;
-        T* home = out + g.idx(gx, gy, 0);
-        const bool col_in = gx < g.n[0], col_full = gx + PXV <= g.n[0];
-#pragma unroll 1
-        for (int side = 0; side < 2; ++side) {
-            if (side == 0 ? !is_lo : !is_hi) continue;
-            const long long z0 = side == 0 ? 0 : g.n[2] - link.face_planes;
-            const long long rdelta = (static_cast<T*>(side == 0 ? link.peer_out_lo : link.peer_out_hi) - out) +
-                                     (side == 0 ? link.shift_lo : link.shift_hi);
-#pragma unroll 1
-            for (int p = 0; p < link.face_planes; ++p) {
-                T* src = home + (z0 + p) * plane_stride;
-#pragma unroll
-                for (int i = 0; i < PY; ++i) {
-                    if ((s_rows & (1u << i)) && col_in && gy + i < g.n[1]) {
-                        if (col_full) {
-                            T v[PXV];
-                            VecN<T, PXV>::ldcg(src + i * g.pitch_x, v);
-                            VecN<T, PXV>::st(src + rdelta + i * g.pitch_x, v);
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < PXV; ++k)
-                                if (gx + k < g.n[0]) src[rdelta + i * g.pitch_x + k] = __ldcg(src + i * g.pitch_x + k);
-                        }
-                    }
-                }
-            }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence_system();
-            if (is_lo) red_release_sys_add_u32(link.signal_lo, 1u);
-            if (is_hi) red_release_sys_add_u32(link.signal_hi, 1u);
-        }
-    }
+    if (LINKED && (is_lo || is_hi))
+        t3r_push_faces<T, PXV, PY>(out, g, link, is_lo, is_hi, gx, gy, s_rows, tid == 0);
 }
 
 template <class T, int R>

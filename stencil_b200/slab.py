@@ -34,8 +34,8 @@ def resolve_kernel(desc: capi.Desc):
     in csrc/capi.cu; max depth is asked from the library)."""
     star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
     w2d = desc.ndim == 2 and (desc.radius == 1 or star_r or (desc.shape == capi.BOX and desc.radius == 2))
-    t3 = desc.ndim == 3 and (desc.radius == 1 or (desc.shape == capi.STAR and (
-        desc.radius == 2 or (3 <= desc.radius <= 4 and desc.dtype == capi.F64))))
+    t3 = desc.ndim == 3 and (desc.radius <= 2 or (desc.shape == capi.STAR and 3 <= desc.radius <= 4
+                                                  and desc.dtype == capi.F64))
     l1 = desc.ndim == 1 and desc.radius <= 4
     sep9 = desc.shape == capi.BOX and bool(desc.flags & capi.FLAG_REASSOCIATE)     # separable 9-point box
     kern = desc.kernel

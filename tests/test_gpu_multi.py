@@ -188,7 +188,9 @@ def _single_gpu_digest(n, r, shape, dtype, T):
     ((257, 240), 2, capi.STAR, capi.F64, 5, 2),        # warp2dr radius 2
     ((200, 180), 2, capi.BOX, capi.F32, 6, 3),         # 25-point box, three slabs
     ((96, 80, 48), 2, capi.STAR, capi.F64, 5, 3),      # 13-point star (tma3dr), three slabs
-    ((64, 48, 40), 2, capi.BOX, capi.F64, 3, 1),       # generic kernel: one GPU only
+    ((64, 48, 40), 2, capi.BOX, capi.F64, 3, 2),       # 125-point box (tma3db), two slabs
+    ((72, 50, 36), 2, capi.BOX, capi.F32, 4, 3),       # the same in fp32, three slabs
+    ((64, 48, 40), 3, capi.BOX, capi.F64, 3, 1),       # generic kernel: one GPU only
 ])
 def test_group_sweep_digest_equals_one_gpu(multi, n, r, shape, dtype, T, G):
     L = multi(max(G, 2))
@@ -207,7 +209,7 @@ def test_group_sweep_digest_equals_one_gpu(multi, n, r, shape, dtype, T, G):
 def test_group_sweep_rejects_what_it_cannot_link(multi):
     L = multi(2)
     res = capi.GroupResult()
-    d = capi.make_desc((64, 48, 40), 2, capi.BOX, capi.F64, 3, ngpus=2)      # generic kernel has no fused exchange
+    d = capi.make_desc((64, 48, 40), 3, capi.BOX, capi.F64, 3, ngpus=2)      # generic kernel has no fused exchange
     assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_UNSUPPORTED
     d = capi.make_desc((64, 48, 41), 1, capi.STAR, capi.F64, 3, ngpus=2)     # 41 planes over 2 GPUs
     assert L.sb200_group_sweep(ctypes.byref(d), capi.INIT_REF, 0, 0, ctypes.byref(res)) == capi.ERR_INVALID

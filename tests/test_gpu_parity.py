@@ -193,6 +193,23 @@ def test_tma3d_radius2_star_kernel(gpu, n, T, r, dtype):
     assert _check(n, r, capi.STAR, dtype, T).kernel == auto
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,T,seed", [
+    ((1, 1, 1), 3, 1), ((5, 4, 3), 4, 1), ((60, 60, 20), 3, 1), ((61, 59, 33), 5, 2), ((130, 70, 40), 2, 1),
+    ((200, 130, 17), 3, 3), ((123, 125, 64), 4, 1), ((300, 64, 9), 2, 1), ((57, 121, 5), 1, 1), ((126, 60, 30), 6, 0),
+    ((240, 50, 12), 3, 1), ((120, 130, 10), 2, 2), ((359, 20, 8), 2, 1),    # fp32: the 128-wide tile variant (fewer columns wasted)
+])
+def test_tma3d_radius2_box_kernel(gpu, n, T, seed, dtype):
+    """125-point box (3-D radius 2) through the TMA kernel of tma3db.cuh (2R+1 running sums per
+    point, each in the oracle's order), bit-exact; AUTO picks it; radius 3 stays generic."""
+    t = _check(n, 2, capi.BOX, dtype, T, seed=seed, kernel=capi.KERNEL_TMA3D)
+    assert t.kernel == capi.KERNEL_TMA3D and t.time_block == 1 and t.launches == T
+    assert _check(n, 2, capi.BOX, dtype, T, seed=seed).kernel == capi.KERNEL_TMA3D
+    a, b = _oracle_pair(n, 3, dtype, seed)
+    with pytest.raises(capi.StencilError):
+        sweep.run_host(n, a, b, T, radius=3, shape=capi.BOX, kernel=capi.KERNEL_TMA3D)
+
+
 @pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float64, 1e-12)])
 @pytest.mark.parametrize("n,T,k,seed", [
     ((1, 1, 1), 3, 2, 1), ((5, 4, 3), 3, 1, 1), ((60, 62, 20), 4, 2, 1), ((61, 59, 33), 3, 1, 2),
@@ -251,7 +268,8 @@ def test_auto_dispatch(gpu):
     assert _check((200, 100), 1, capi.BOX, np.float32, 8).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70, 60), 1, capi.STAR, np.float64, 4).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 1, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
-    assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70, 20), 2, capi.BOX, np.float64, 2).kernel == capi.KERNEL_TMA3D
+    assert _check((80, 70, 20), 3, capi.BOX, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70, 20), 2, capi.STAR, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 3, capi.STAR, np.float64, 2).kernel == capi.KERNEL_TMA3D
     assert _check((80, 70, 20), 5, capi.STAR, np.float64, 2).kernel == capi.KERNEL_GENERIC
@@ -347,7 +365,7 @@ def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     axis.  For T <= n_outer that equals the middle copy of three stacked copies swept with the
     ordinary Dirichlet oracle, bit for bit."""
     import torch
-    if shape == capi.BOX and (r > 2 or (r >= 2 and len(n) == 3)):
+    if shape == capi.BOX and r > 2:
         pytest.skip("no fused box kernel at this radius")
     if len(n) == 3 and r >= 3 and dtype == np.float32:
         pytest.skip("AUTO keeps the generic kernel for 3-D radius 3..4 in fp32")

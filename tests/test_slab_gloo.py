@@ -196,7 +196,8 @@ def test_resolve_kernel_defaults():
     assert slab.resolve_kernel(capi.make_desc((8, 8), shape=capi.BOX)) == (capi.KERNEL_WARP2D, 4)
     assert slab.resolve_kernel(capi.make_desc((8, 8, 8), shape=capi.BOX)) == (capi.KERNEL_TMA3D, 2)
     assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=2)) == (capi.KERNEL_TMA3D, 1)
-    assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=2, shape=capi.BOX)) == (capi.KERNEL_GENERIC, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=2, shape=capi.BOX)) == (capi.KERNEL_TMA3D, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=3, shape=capi.BOX)) == (capi.KERNEL_GENERIC, 1)
     assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=3, dtype=capi.F64)) == (capi.KERNEL_TMA3D, 1)
     assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=3)) == (capi.KERNEL_GENERIC, 1)
     assert slab.resolve_kernel(capi.make_desc((8, 8, 8), radius=5)) == (capi.KERNEL_GENERIC, 1)

@@ -5,5 +5,5 @@ set -e
 tag=$1; shift
 cd "$(dirname "$0")/../stencil_b200/csrc"
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -cudart static "$@" -c -o /tmp/capi_$tag.o capi.cu
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -Xcompiler -fPIC -cudart static -o ../libstencil_b200_$tag.so /tmp/capi_$tag.o resident2d.o warp2d.o
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -Xcompiler -fPIC -cudart static -o ../libstencil_b200_$tag.so /tmp/capi_$tag.o resident2d.o warp2d.o tma3db.o
 echo built $tag

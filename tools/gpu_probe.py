@@ -89,6 +89,12 @@ if "box2" in which:  # 25-point box: fused warp kernel vs one launch per step
                     capi.make_desc((8192, 8192), 2, capi.BOX, dt, 24, kernel=capi.KERNEL_WARP2D))):
                 run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 24, capi.KERNEL_WARP2D, k, r=2)
         run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 8, capi.KERNEL_GENERIC, 1, r=2)
+if "box3" in which:  # 3-D box radius 2 (125-point): which kernel, and how far from the FP-add bound
+    for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
+        run(f"125pt-{nm}", (512, 512, 256), capi.BOX, dt, 4, capi.KERNEL_GENERIC, 1, r=2)
+        run(f"125pt-{nm}", (512, 512, 256), capi.BOX, dt, 4, capi.KERNEL_TMA3D, 1, r=2)
+        run(f"125pt-{nm}", (512, 512, 512), capi.BOX, dt, 4, capi.KERNEL_AUTO, 0, r=2)
+        run(f"343pt-{nm}", (256, 256, 256), capi.BOX, dt, 4, capi.KERNEL_GENERIC, 1, r=3)
 if "line" in which:  # 1-D: fused register kernel vs one launch per step
     for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
         for r in (1, 4):

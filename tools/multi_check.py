@@ -31,6 +31,7 @@ CASES = [  # n_local, radius, shape, dtype, T, k, exchange
     ((640, 256), 3, capi.STAR, capi.F64, 5, 2, "p2p"),
     ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "nccl"),  # 13-point star (tma3dr)
     ((200, 160, 48), 2, capi.STAR, capi.F64, 5, 1, "p2p"),
+    ((200, 160, 48), 2, capi.BOX, capi.F32, 4, 1, "p2p"),    # 125-point box (tma3db)
     ((200, 160, 48), 3, capi.STAR, capi.F64, 4, 1, "p2p"),   # 19-point star (fp64: where AUTO takes the TMA kernel)
     ((200, 160, 48), 2, capi.BOX, capi.F32, 3, 1, "nccl"),   # 125-point box: generic kernel, NCCL only
 ]

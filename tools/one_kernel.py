@@ -1,5 +1,5 @@
 """Run one config a few passes (for ncu captures):
-tools/one_kernel.py c1|c1f32|c2|c3|c4|c2gen|res512|rad2|rad3f64|line|linef64 [k]"""
+tools/one_kernel.py c1|c1f32|c2|c3|c4|c2gen|res512|rad2|rad3f64|box3f32|box3f64|line|linef64 [k]"""
 import os
 import sys
 
@@ -13,8 +13,9 @@ CFG = {"c1": ((4096, 4096), capi.STAR, capi.F64, 4), "c1f32": ((4096, 4096), cap
        "c4": ((16384, 16384), capi.BOX, capi.F32, 4),
        "c2gen": ((512, 512, 512), capi.STAR, capi.F64, 1), "res512": ((512, 512), capi.STAR, capi.F32, 0),
        "rad2": ((8192, 8192), capi.STAR, capi.F32, 4), "rad3f64": ((8192, 8192), capi.STAR, capi.F64, 2),
+       "box3f32": ((512, 512, 512), capi.BOX, capi.F32, 1), "box3f64": ((512, 512, 512), capi.BOX, capi.F64, 1),
        "line": ((1 << 27,), capi.STAR, capi.F32, 16), "linef64": ((1 << 27,), capi.STAR, capi.F64, 16)}
-RADIUS = {"rad2": 2, "rad3f64": 3}
+RADIUS = {"rad2": 2, "rad3f64": 3, "box3f32": 2, "box3f64": 2}
 name = sys.argv[1]
 n, shape, dtype, k = CFG[name]
 if len(sys.argv) > 2:
