@@ -80,6 +80,7 @@ def test_bmp_dump(built, tmp_path):
     ["-s", 1, "-i", 6, "-b", 1, "--shape", "160,120,90", "--dtype", "f64", "--init", "random"],
     ["-s", 300, "-i", 12, "-b", 1, "--stencil", "box", "--init", "random"],
     ["-s", 200, "-i", 5, "-b", 1, "-r", 3],
+    ["-s", 1, "-i", 3, "-b", 1, "--shape", "130,70,40", "-r", 2, "--stencil", "box", "--dtype", "f64", "--init", "random"],  # 125-point
     ["-s", 1, "-i", 37, "-b", 1, "--shape", "100003", "-r", 2, "--dtype", "f64", "--init", "random"],  # 1-D
     ["-s", 1, "-i", 10, "-b", 1, "--shape", "4096", "--stencil", "box", "--kernel", "line1d"],
 ])
