@@ -295,8 +295,8 @@ def test_zero_iterations_is_identity(gpu):
 
 
 def test_unsupported_kernel_request_is_an_error(gpu):
-    d = capi.make_desc((8, 8, 8), radius=2, shape=capi.BOX, kernel=capi.KERNEL_TMA3D)   # 125-point: generic only
-    a = np.zeros((12, 12, 12), np.float32)
+    d = capi.make_desc((8, 8, 8), radius=3, shape=capi.BOX, kernel=capi.KERNEL_TMA3D)   # 343-point: generic only
+    a = np.zeros((14, 14, 14), np.float32)
     rc = capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, a.ctypes.data, None)
     assert rc == capi.ERR_UNSUPPORTED
 
