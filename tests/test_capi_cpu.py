@@ -103,6 +103,15 @@ def test_plan_host_logic(monkeypatch):
     p = capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F64, 100), 100)
     assert (p.kernel, p.time_block) == (capi.KERNEL_WARP2D, 1)
     assert capi.plan(capi.make_desc((400, 400), 3, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    # 125-point box (3-D radius 2): TMA kernel, one step per launch; fp64 tiles store 60 x 60, fp32 tiles
+    # 120 x 60 or 56 x 124, whichever computes fewer columns for this row length
+    p = capi.plan(capi.make_desc((512, 512, 512), 2, capi.BOX, capi.F64, 4), 4)
+    assert (p.kernel, p.time_block, p.launches, p.tiles_x, p.tiles_y) == (capi.KERNEL_TMA3D, 1, 4, 9, 9)
+    p = capi.plan(capi.make_desc((512, 512, 512), 2, capi.BOX, capi.F32, 4), 4)
+    assert (p.kernel, p.tiles_x, p.tiles_y) == (capi.KERNEL_TMA3D, 5, 9)             # 5 x 128 = 10 x 64: the wide tile
+    p = capi.plan(capi.make_desc((130, 70, 40), 2, capi.BOX, capi.F32, 4), 4)
+    assert (p.kernel, p.tiles_x, p.tiles_y) == (capi.KERNEL_TMA3D, 3, 1)             # 3 x 64 < 2 x 128: the narrow tile
+    assert capi.plan(capi.make_desc((64, 64, 64), 3, capi.BOX, capi.F32, 4), 4).kernel == capi.KERNEL_GENERIC
     assert capi.plan(capi.make_desc((400, 400), 5, capi.STAR, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     # 1-D: warp segments of 512 points; 16 fused steps by default at r=1 (10 here: one launch,
     # 512 - 12 - 10 -> 488 stored per segment), 8 at r=4
