@@ -451,10 +451,12 @@ struct Choice {
     int k;
 };
 
-// WARP2D family: radius 1 star/box (warp2d.cuh), radius 2..4 star (warp2dr.cuh).
-bool warp2d_supports(const sb200_desc* d) {
-    return d->ndim == 2 && (d->radius == 1 || (d->shape == SB200_STAR && d->radius >= 2 && d->radius <= 4) ||
-                            (d->shape == SB200_BOX && d->radius == 2));
+// WARP2D family: radius 1 star/box (warp2d.cuh), radius 2..4 star and box (warp2dr.cuh).
+bool warp2d_supports(const sb200_desc* d) { return d->ndim == 2 && d->radius >= 1 && d->radius <= 4; }
+// What AUTO takes from it: the 81-point box in fp32 runs at 202 registers per thread and loses to the
+// generic kernel (198 vs 221 GStencil/s, profiles/r02u_box2d_probe.log); every other case wins.
+bool warp2d_preferred(const sb200_desc* d) {
+    return warp2d_supports(d) && !(d->shape == SB200_BOX && d->radius == 4 && d->dtype == SB200_F32);
 }
 
 // TMA3D family: radius 1 star / box (tma3d.cuh), radius 2..4 star (tma3dr.cuh), radius 2 box (tma3db.cuh).
@@ -481,7 +483,7 @@ int t3_shape(const sb200_desc* d) {
 
 Choice choose(const sb200_desc* d) {
     Choice c;
-    const bool w2d_ok = warp2d_supports(d);
+    const bool w2d_ok = warp2d_preferred(d);
     const bool t3_ok = tma3d_preferred(d);
     const bool l1_ok = d->ndim == 1 && d->radius <= 4;
     int kern = d->kernel;

@@ -21,7 +21,8 @@
 
 namespace sb200 {
 
-__host__ __device__ constexpr int w2r_depth(int R) { return R == 3 ? 9 : 8; }  // ring slots, multiple of R
+// ring slots: a multiple of the level's phase count (star: R, box: 2R)
+__host__ __device__ constexpr int w2r_depth(int R, int shape = STAR) { return R == 3 ? (shape == BOX ? 6 : 9) : 8; }
 __host__ __device__ constexpr int w2r_halo_left(int K, int R) { return (K * R + 3) & ~3; }
 __host__ __device__ constexpr int w2r_valid(int K, int R) { return (W2D_WIDTH - w2r_halo_left(K, R) - K * R) & ~3; }
 // deepest fusion per radius and element size (register budget: 8R state registers per level
@@ -73,7 +74,10 @@ template <class T, int R> struct W2rLevel {
 // y' = y-R .. y+R, so 2R+1 accumulator chains advance by its 2R+1 window values each; output
 // y-R completes and output y+R opens in the same slot (slots = row index mod 2R).  Same lag of
 // R rows per level as the star, so the streaming code is shared.
-__host__ __device__ constexpr int w2r_box_max_k(int R, int elem_size) { return R == 2 ? (elem_size == 4 ? 2 : 1) : 0; }
+// Radius 3 and 4 (49- and 81-point): 2R accumulator chains + R rows of state per point leave room for one level.
+__host__ __device__ constexpr int w2r_box_max_k(int R, int elem_size) {
+    return R == 2 ? (elem_size == 4 ? 2 : 1) : (R == 3 || R == 4 ? 1 : 0);
+}
 
 template <class T, int R> struct W2rBoxLevel {
     static constexpr int PHASES = 2 * R;
@@ -119,9 +123,9 @@ __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restr
                                            int nsteps, int j_dom_lo, int j_dom_hi, int j_row_lo,
                                            int j_row_hi, unsigned mxmask, T* ring, bool lane_valid,
                                            int ncols_valid, T avg) {
-    constexpr int D = w2r_depth(R);
+    constexpr int D = w2r_depth(R, SHAPE);
     constexpr int PH = W2rLevelSel<T, R, SHAPE>::PHASES;
-    static_assert(D % PH == 0 && PH <= 4, "the row loop is unrolled by a multiple of the phase count");
+    static_assert(D % PH == 0 && PH <= 8, "the row loop is unrolled by a multiple of the phase count");
     typename W2rLevelSel<T, R, SHAPE>::type lv[K];
 #pragma unroll
     for (int l = 0; l < K; ++l) lv[l].init();
@@ -168,7 +172,11 @@ __device__ __forceinline__ void w2r_stream(const T* __restrict__ src, T* __restr
                     case 0: lv[l].template step<0, EDGE>(w, avg, upd, o); break;
                     case 1: lv[l].template step<1 % PH, EDGE>(w, avg, upd, o); break;
                     case 2: lv[l].template step<2 % PH, EDGE>(w, avg, upd, o); break;
-                    default: lv[l].template step<3 % PH, EDGE>(w, avg, upd, o); break;
+                    case 3: lv[l].template step<3 % PH, EDGE>(w, avg, upd, o); break;
+                    case 4: lv[l].template step<4 % PH, EDGE>(w, avg, upd, o); break;
+                    case 5: lv[l].template step<5 % PH, EDGE>(w, avg, upd, o); break;
+                    case 6: lv[l].template step<6 % PH, EDGE>(w, avg, upd, o); break;
+                    default: lv[l].template step<7 % PH, EDGE>(w, avg, upd, o); break;
                 }
                 cur = o;
             }
@@ -195,7 +203,7 @@ sweep_warp2dr_kernel(const T* __restrict__ in, T* __restrict__ out, Grid g, Doma
                      T avg, const SlabLinkDev link) {
     constexpr int HL = w2r_halo_left(K, R);
     constexpr int V = w2r_valid(K, R);
-    constexpr int D = w2r_depth(R);
+    constexpr int D = w2r_depth(R, SHAPE);
     const int lane = threadIdx.x & 31;
     const long long item = (long long)blockIdx.x * W2D_WARPS + (threadIdx.x >> 5);
     if (item >= nitems) return;
@@ -273,13 +281,15 @@ static cudaError_t launch_warp2dr_k(const T* in, T* out, const Grid& g, Domain d
     return cudaGetLastError();
 }
 
-// 2-D star, radius 2..4, K fused steps (1 .. w2r_max_k(R, sizeof(T))); 2-D box, radius 2
-// (25-point), K fused steps (1 .. w2r_box_max_k).
+// 2-D star, radius 2..4, K fused steps (1 .. w2r_max_k(R, sizeof(T))); 2-D box, radius 2..4
+// (25-, 49-, 81-point), K fused steps (1 .. w2r_box_max_k).
 template <class T>
 static cudaError_t launch_warp2dr(const T* in, T* out, const Grid& g, int shape, Domain dom, int K, long long ob,
                                   long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link = nullptr) {
     if (shape == BOX) {
-        if (g.r != 2 || K < 1 || K > w2r_box_max_k(2, (int)sizeof(T))) return cudaErrorInvalidValue;
+        if (g.r < 2 || g.r > 4 || K < 1 || K > w2r_box_max_k(g.r, (int)sizeof(T))) return cudaErrorInvalidValue;
+        if (g.r == 3) return launch_warp2dr_k<T, 3, 1, BOX>(in, out, g, dom, ob, oe, tn, st, link);
+        if (g.r == 4) return launch_warp2dr_k<T, 4, 1, BOX>(in, out, g, dom, ob, oe, tn, st, link);
         if (K == 1) return launch_warp2dr_k<T, 2, 1, BOX>(in, out, g, dom, ob, oe, tn, st, link);
         if constexpr (w2r_box_max_k(2, (int)sizeof(T)) >= 2)
             return launch_warp2dr_k<T, 2, 2, BOX>(in, out, g, dom, ob, oe, tn, st, link);

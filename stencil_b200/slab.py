@@ -32,8 +32,8 @@ _KERNEL_NAMES = {capi.KERNEL_GENERIC: "generic", capi.KERNEL_WARP2D: "warp2d",
 def resolve_kernel(desc: capi.Desc):
     """(family, fused depth) the library will use for this descriptor (mirrors choose()
     in csrc/capi.cu; max depth is asked from the library)."""
-    star_r = desc.shape == capi.STAR and 2 <= desc.radius <= 4
-    w2d = desc.ndim == 2 and (desc.radius == 1 or star_r or (desc.shape == capi.BOX and desc.radius == 2))
+    w2d = desc.ndim == 2 and 1 <= desc.radius <= 4 and not (
+        desc.shape == capi.BOX and desc.radius == 4 and desc.dtype == capi.F32)
     t3 = desc.ndim == 3 and (desc.radius <= 2 or (desc.shape == capi.STAR and 3 <= desc.radius <= 4
                                                   and desc.dtype == capi.F64))
     l1 = desc.ndim == 1 and desc.radius <= 4

@@ -102,7 +102,9 @@ def test_plan_host_logic(monkeypatch):
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 2, 50)   # 25-point box: fused warp kernel
     p = capi.plan(capi.make_desc((400, 400), 2, capi.BOX, capi.F64, 100), 100)
     assert (p.kernel, p.time_block) == (capi.KERNEL_WARP2D, 1)
-    assert capi.plan(capi.make_desc((400, 400), 3, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    p = capi.plan(capi.make_desc((400, 400), 3, capi.BOX, capi.F32, 100), 100)
+    assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 1, 100)  # 49-point box: warp kernel, one level
+    assert capi.plan(capi.make_desc((400, 400), 5, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
     # 125-point box (3-D radius 2): TMA kernel, one step per launch; fp64 tiles store 60 x 60, fp32 tiles
     # 120 x 60 or 56 x 124, whichever computes fewer columns for this row length
     p = capi.plan(capi.make_desc((512, 512, 512), 2, capi.BOX, capi.F64, 4), 4)

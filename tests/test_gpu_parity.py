@@ -150,9 +150,25 @@ def test_warp2d_radius2_box_kernel(gpu, n, T, k, dtype):
     assert t.kernel == capi.KERNEL_WARP2D and t.time_block == ke and t.launches == -(-T // ke)
 
 
-def test_warp2d_radius3_box_is_unsupported(gpu):
-    d = capi.make_desc((64, 64), radius=3, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
-    a = np.zeros((70, 70), np.float32)
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("r", [3, 4])
+@pytest.mark.parametrize("n,T,seed", [
+    ((1, 1), 3, 1), ((3, 2), 5, 1), ((120, 50), 4, 1), ((121, 97), 6, 2), ((250, 31), 5, 1),
+    ((1000, 129), 4, 3), ((113, 113), 8, 1), ((64, 700), 3, 1), ((300, 300), 12, 0),
+])
+def test_warp2d_radius34_box_kernel(gpu, n, T, r, seed, dtype):
+    """49- / 81-point box (2-D radius 3, 4) through the warp kernel (2R+1 chains, one level per
+    launch), bit-exact; AUTO picks it; radius 5 is the generic kernel's."""
+    t = _check(n, r, capi.BOX, dtype, T, seed=seed, kernel=capi.KERNEL_WARP2D)
+    assert t.kernel == capi.KERNEL_WARP2D and t.time_block == 1 and t.launches == T
+    # AUTO picks it except for the 81-point box in fp32, where the generic kernel is faster
+    auto = capi.KERNEL_GENERIC if (r == 4 and dtype == np.float32) else capi.KERNEL_WARP2D
+    assert _check(n, r, capi.BOX, dtype, T, seed=seed).kernel == auto
+
+
+def test_warp2d_radius5_box_is_unsupported(gpu):
+    d = capi.make_desc((64, 64), radius=5, shape=capi.BOX, kernel=capi.KERNEL_WARP2D)
+    a = np.zeros((74, 74), np.float32)
     assert capi.lib().sb200_run_host(ctypes.byref(d), a.ctypes.data, a.ctypes.data, None) == capi.ERR_UNSUPPORTED
 
 
@@ -275,7 +291,9 @@ def test_auto_dispatch(gpu):
     assert _check((80, 70, 20), 5, capi.STAR, np.float64, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 2, capi.STAR, np.float32, 2).kernel == capi.KERNEL_WARP2D
     assert _check((80, 70), 2, capi.BOX, np.float32, 2).kernel == capi.KERNEL_WARP2D
-    assert _check((80, 70), 3, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
+    assert _check((80, 70), 3, capi.BOX, np.float32, 2).kernel == capi.KERNEL_WARP2D
+    assert _check((80, 70), 4, capi.BOX, np.float64, 2).kernel == capi.KERNEL_WARP2D
+    assert _check((80, 70), 5, capi.BOX, np.float32, 2).kernel == capi.KERNEL_GENERIC
     assert _check((80, 70), 5, capi.STAR, np.float32, 2).kernel == capi.KERNEL_GENERIC
     assert _check((3000,), 2, capi.BOX, np.float64, 9).kernel == capi.KERNEL_LINE1D
     assert _check((3000,), 6, capi.STAR, np.float32, 3).kernel == capi.KERNEL_GENERIC
@@ -365,10 +383,12 @@ def test_slab_link_self_periodic(gpu, n, r, T, k, shape, dtype):
     axis.  For T <= n_outer that equals the middle copy of three stacked copies swept with the
     ordinary Dirichlet oracle, bit for bit."""
     import torch
-    if shape == capi.BOX and r > 2:
+    if shape == capi.BOX and r > 2 and len(n) == 3:
         pytest.skip("no fused box kernel at this radius")
     if len(n) == 3 and r >= 3 and dtype == np.float32:
         pytest.skip("AUTO keeps the generic kernel for 3-D radius 3..4 in fp32")
+    if len(n) == 2 and r == 4 and shape == capi.BOX and dtype == np.float32:
+        pytest.skip("AUTO keeps the generic kernel for the 81-point box in fp32")
     d = capi.make_desc(n, r, shape, capi.F64 if dtype == np.float64 else capi.F32, T, time_block=k)
     k = min(k, int(capi.lib().sb200_max_time_block(ctypes.byref(d))))
     no = n[-1]

@@ -177,7 +177,7 @@ def test_exchange_mode_selection():
     d2 = capi.make_desc((8, 16), shape=capi.BOX)
     d2r = capi.make_desc((8, 32), radius=2)
     d3r = capi.make_desc((8, 8, 16), radius=2)
-    d2g = capi.make_desc((8, 32), radius=3, shape=capi.BOX)
+    d2g = capi.make_desc((8, 48), radius=5, shape=capi.BOX)
     assert slab.SlabSweep(d3, 0, 1, engine_factory=OracleEngine).exchange == "none"
     # the fused exchange exists for the WARP2D family (rows) and the TMA3D family (planes)
     assert slab.SlabSweep(d2, 0, 2, engine_factory=OracleEngine, dist=dist, exchange="p2p").exchange == "p2p"
@@ -205,7 +205,10 @@ def test_resolve_kernel_defaults():
     assert slab.resolve_kernel(capi.make_desc((8, 8), radius=2)) == (capi.KERNEL_WARP2D, 4)
     assert slab.resolve_kernel(capi.make_desc((8, 8), radius=3, dtype=capi.F64, time_block=5)) == (capi.KERNEL_WARP2D, 2)
     assert slab.resolve_kernel(capi.make_desc((8, 8), radius=2, shape=capi.BOX)) == (capi.KERNEL_WARP2D, 2)
-    assert slab.resolve_kernel(capi.make_desc((8, 8), radius=3, shape=capi.BOX)) == (capi.KERNEL_GENERIC, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8), radius=3, shape=capi.BOX)) == (capi.KERNEL_WARP2D, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8), radius=5, shape=capi.BOX)) == (capi.KERNEL_GENERIC, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8), radius=4, shape=capi.BOX)) == (capi.KERNEL_GENERIC, 1)
+    assert slab.resolve_kernel(capi.make_desc((8, 8), radius=4, shape=capi.BOX, dtype=capi.F64)) == (capi.KERNEL_WARP2D, 1)
     assert slab.resolve_kernel(capi.make_desc((800,), radius=3)) == (capi.KERNEL_LINE1D, 10)
     assert slab.resolve_kernel(capi.make_desc((800,), radius=5)) == (capi.KERNEL_GENERIC, 1)
 

@@ -14,8 +14,8 @@ capi.check(capi.lib().sb200_init(0))
 PEAK = 6529.1
 
 
-def run(name, n, shape, dtype, T, kernel, k, reps=3, r=1, flags=0):
-    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel, flags=flags)
+def run(name, n, shape, dtype, T, kernel, k, reps=3, r=1, flags=0, hint=0):
+    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel, flags=flags | (capi.FLAG_BLOCK_TILE if hint else 0), block_hint=hint)
     try:
         g = sweep.DeviceGrids(d)
         g.fill(capi.INIT_RANDOM, seed=1)
@@ -59,6 +59,11 @@ if "c4" in which:
     for k in (1, 2, 4, 6):
         run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k)
     run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 6, capi.KERNEL_GENERIC, 1)
+if "c1tile" in which:  # config 1 (and its fp32 twin): rows per warp (SB200_FLAG_BLOCK_TILE) against the planner's choice
+    for dt, nm in ((capi.F64, "f64"), (capi.F32, "f32")):
+        for k in (4, 6):
+            for rows in (0, 32, 48, 64, 82, 96, 128, 164, 256):
+                run(f"c1-{nm}-rows{rows}", (4096, 4096), capi.STAR, dt, 96, capi.KERNEL_WARP2D, k, hint=rows)
 if "sep9" in which:  # separable 9-point box (SB200_FLAG_REASSOCIATE) against the reference-order level
     for dt, nm, n in ((capi.F32, "f32", 16384), (capi.F64, "f64", 8192)):
         for k in (2, 4, 6):
@@ -89,6 +94,9 @@ if "box2" in which:  # 25-point box: fused warp kernel vs one launch per step
                     capi.make_desc((8192, 8192), 2, capi.BOX, dt, 24, kernel=capi.KERNEL_WARP2D))):
                 run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 24, capi.KERNEL_WARP2D, k, r=2)
         run(f"box2-{nm}", (8192, 8192), capi.BOX, dt, 8, capi.KERNEL_GENERIC, 1, r=2)
+        for r in (3, 4):  # 49- and 81-point
+            run(f"box{r}-{nm}", (8192, 8192), capi.BOX, dt, 8, capi.KERNEL_WARP2D, 1, r=r)
+            run(f"box{r}-{nm}", (8192, 8192), capi.BOX, dt, 4, capi.KERNEL_GENERIC, 1, r=r)
 if "box3" in which:  # 3-D box radius 2 (125-point): which kernel, and how far from the FP-add bound
     for dt, nm in ((capi.F32, "f32"), (capi.F64, "f64")):
         run(f"125pt-{nm}", (512, 512, 256), capi.BOX, dt, 4, capi.KERNEL_GENERIC, 1, r=2)
