@@ -362,6 +362,11 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
     long long nchunks = (want_items + p.nstrips - 1) / p.nstrips;
     long long chunk_rows = (rows + nchunks - 1) / nchunks;
     const long long min_rows = 16LL * K * R;
+    // Large grids: more, shorter chunks balance the SMs better than few long ones, up to the point
+    // where the 2KR redundant rows per chunk cost more than the balance gains — measured on config 4
+    // (16384^2, profiles/r02t_c4_tile_probe.log): 150-300 rows beat the 469 of the rule above by 8-14 %.
+    const long long max_rows = 40LL * K * R;  // 5 % redundant rows
+    if (chunk_rows > max_rows) chunk_rows = max_rows;
     const bool small = ((rows + min_rows - 1) / min_rows) * p.nstrips < (long long)sm_count * 8;
     if (chunk_rows < min_rows && !small) chunk_rows = min_rows;
     if (chunk_rows < min_rows && small) {

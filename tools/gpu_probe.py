@@ -64,6 +64,12 @@ if "c1tile" in which:  # config 1 (and its fp32 twin): rows per warp (SB200_FLAG
         for k in (4, 6):
             for rows in (0, 32, 48, 64, 82, 96, 128, 164, 256):
                 run(f"c1-{nm}-rows{rows}", (4096, 4096), capi.STAR, dt, 96, capi.KERNEL_WARP2D, k, hint=rows)
+if "c4tile" in which:  # config 4: rows per warp against the planner's choice
+    for k in (4, 6):
+        for rows in (0, 64, 100, 128, 150, 200, 250, 300, 350, 400, 469, 600, 781, 1024, 1600):
+            run(f"c4-rows{rows}", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k, hint=rows)
+        for rows in (0, 150, 200, 250, 300, 400, 781):
+            run(f"c4-sep-rows{rows}", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k, hint=rows, flags=capi.FLAG_REASSOCIATE)
 if "sep9" in which:  # separable 9-point box (SB200_FLAG_REASSOCIATE) against the reference-order level
     for dt, nm, n in ((capi.F32, "f32", 16384), (capi.F64, "f64", 8192)):
         for k in (2, 4, 6):
