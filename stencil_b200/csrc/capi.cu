@@ -453,8 +453,8 @@ struct Choice {
 
 // WARP2D family: radius 1 star/box (warp2d.cuh), radius 2..4 star and box (warp2dr.cuh).
 bool warp2d_supports(const sb200_desc* d) { return d->ndim == 2 && d->radius >= 1 && d->radius <= 4; }
-// What AUTO takes from it: the 81-point box in fp32 runs at 202 registers per thread and loses to the
-// generic kernel (198 vs 221 GStencil/s, profiles/r02u_box2d_probe.log); every other case wins.
+// What AUTO takes from it: the 81-point box in fp32 loses to the generic kernel (198 vs 221 GStencil/s,
+// profiles/r02u_box2d_probe.log); every other case wins.
 bool warp2d_preferred(const sb200_desc* d) {
     return warp2d_supports(d) && !(d->shape == SB200_BOX && d->radius == 4 && d->dtype == SB200_F32);
 }
