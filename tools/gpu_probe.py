@@ -64,6 +64,11 @@ if "c1tile" in which:  # config 1 (and its fp32 twin): rows per warp (SB200_FLAG
         for k in (4, 6):
             for rows in (0, 32, 48, 64, 82, 96, 128, 164, 256):
                 run(f"c1-{nm}-rows{rows}", (4096, 4096), capi.STAR, dt, 96, capi.KERNEL_WARP2D, k, hint=rows)
+if "c2tile" in which:  # configs 2 / 3 / 5-slab: planes per CTA against the planner's makespan search
+    for nm, n, shp, dt in (("c2", (512, 512, 512), capi.STAR, capi.F64), ("c3", (512, 512, 512), capi.BOX, capi.F64),
+                           ("c5slab", (1024, 1024, 256), capi.STAR, capi.F64), ("c2f32", (512, 512, 512), capi.STAR, capi.F32)):
+        for planes in (0, 16, 24, 32, 40, 48, 56, 64, 86, 103, 128, 171, 256):
+            run(f"{nm}-planes{planes}", n, shp, dt, 24, capi.KERNEL_TMA3D, 2, hint=planes)
 if "c4tile" in which:  # config 4: rows per warp against the planner's choice
     for k in (4, 6):
         for rows in (0, 64, 100, 128, 150, 200, 250, 300, 350, 400, 469, 600, 781, 1024, 1600):
