@@ -16,8 +16,8 @@ from stencil_b200 import capi, sweep
 pytestmark = pytest.mark.gpu
 
 
-def _gpu_checksum(n, shape, dtype, T, k=0, kernel=capi.KERNEL_AUTO, seed=1):
-    d = capi.make_desc(n, 1, shape, dtype, T, time_block=k, kernel=kernel)
+def _gpu_checksum(n, shape, dtype, T, k=0, kernel=capi.KERNEL_AUTO, seed=1, r=1):
+    d = capi.make_desc(n, r, shape, dtype, T, time_block=k, kernel=kernel)
     g = sweep.DeviceGrids(d)
     g.fill(capi.INIT_RANDOM, seed=seed)
     g.sweep(T)
@@ -71,6 +71,24 @@ def test_config5_full_grid_is_independent_of_kernel_and_depth(gpu):
     ref = _gpu_checksum(n, capi.STAR, capi.F64, T, k=2)
     assert _gpu_checksum(n, capi.STAR, capi.F64, T, k=1) == ref
     assert _gpu_checksum(n, capi.STAR, capi.F64, T, kernel=capi.KERNEL_GENERIC) == ref
+
+
+@pytest.mark.parametrize("name,n,r,shape,dtype,T,fused", [
+    ("125-point f64", (512, 512, 256), 2, capi.BOX, capi.F64, 4, capi.KERNEL_TMA3D),
+    ("125-point f32, narrow tiles", (300, 512, 256), 2, capi.BOX, capi.F32, 4, capi.KERNEL_TMA3D),
+    ("125-point f32, wide tiles", (480, 500, 200), 2, capi.BOX, capi.F32, 3, capi.KERNEL_TMA3D),
+    ("13-point f64", (512, 512, 256), 2, capi.STAR, capi.F64, 5, capi.KERNEL_TMA3D),
+    ("25-point f32", (8192, 4096), 2, capi.BOX, capi.F32, 8, capi.KERNEL_WARP2D),
+    ("49-point f64", (4096, 4096), 3, capi.BOX, capi.F64, 5, capi.KERNEL_WARP2D),
+    ("81-point f32", (4096, 4096), 4, capi.BOX, capi.F32, 4, capi.KERNEL_WARP2D),
+    ("17-point star f32", (8192, 4096), 4, capi.STAR, capi.F32, 8, capi.KERNEL_WARP2D),
+])
+def test_radius_kernels_agree_with_the_generic_kernel_at_size(gpu, name, n, r, shape, dtype, T, fused):
+    """Radius > 1 at sizes the oracle would need minutes for: the fused / TMA kernel and the
+    one-thread-per-point generic kernel (different tilings, different data paths, the same per-point
+    order) give the same bits; the small-size tests pin both against the oracle."""
+    assert (_gpu_checksum(n, shape, dtype, T, kernel=fused, r=r)
+            == _gpu_checksum(n, shape, dtype, T, kernel=capi.KERNEL_GENERIC, r=r)), name
 
 
 def test_linearity_of_the_sweep(gpu):
