@@ -149,63 +149,63 @@ sweep_tma3db_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_const
         const int st = j & (S - 1);
         const int pe = j - R;  // local index of the plane this step finishes (slot 0)
         const bool storing = pe >= R && pe < nin - R;
-        if (warp_on) {
-        mbar_wait(&bars[st], (uint32_t)(j / S) & 1u);
-        const T* src = ring + (size_t)st * C::PLANE + (ly - R) * C::BX + lx;
+        if (warp_on) {  // (warp-uniform)
+            mbar_wait(&bars[st], (uint32_t)(j / S) & 1u);
+            const T* src = ring + (size_t)st * C::PLANE + (ly - R) * C::BX + lx;
 #pragma unroll
-        for (int a = 0; a < PY + 2 * R; ++a) {
-            const int ra = a < row_lo ? row_lo : (a > row_hi ? row_hi : a);
-            T w[PXV + 2 * R];
-            {
-                T c[PXV];
-                VecN<T, PXV>::ld(src + ra * C::BX, c);
+            for (int a = 0; a < PY + 2 * R; ++a) {
+                const int ra = a < row_lo ? row_lo : (a > row_hi ? row_hi : a);
+                T w[PXV + 2 * R];
+                {
+                    T c[PXV];
+                    VecN<T, PXV>::ld(src + ra * C::BX, c);
 #pragma unroll
-                for (int m = 0; m < PXV; ++m) w[R + m] = c[m];
-                auto fill = [&](auto self, auto Kc) {
-                    constexpr int k = decltype(Kc)::value;
-                    if constexpr (k <= R) {
-                        w[R - k] = t3r_at<-k, T, PXV>(c);                    // x - k of element 0
-                        w[R + PXV - 1 + k] = t3r_at<PXV - 1 + k, T, PXV>(c);  // x + k of element PXV-1
-                        self(self, IC<k + 1>{});
-                    }
-                };
-                fill(fill, IC<1>{});
-            }
-            // this row is row dy = a - R - i of owned row i
+                    for (int m = 0; m < PXV; ++m) w[R + m] = c[m];
+                    auto fill = [&](auto self, auto Kc) {
+                        constexpr int k = decltype(Kc)::value;
+                        if constexpr (k <= R) {
+                            w[R - k] = t3r_at<-k, T, PXV>(c);                    // x - k of element 0
+                            w[R + PXV - 1 + k] = t3r_at<PXV - 1 + k, T, PXV>(c);  // x + k of element PXV-1
+                            self(self, IC<k + 1>{});
+                        }
+                    };
+                    fill(fill, IC<1>{});
+                }
+                // this row is row dy = a - R - i of owned row i
 #pragma unroll
-            for (int i = 0; i < PY; ++i) {
-                if (a - i < 0 || a - i > 2 * R) continue;
+                for (int i = 0; i < PY; ++i) {
+                    if (a - i < 0 || a - i > 2 * R) continue;
 #pragma unroll
-                for (int m = 0; m < PXV; ++m)
+                    for (int m = 0; m < PXV; ++m)
 #pragma unroll
-                    for (int dx = 0; dx <= 2 * R; ++dx) {
-                        const T v = w[m + dx];
+                        for (int dx = 0; dx <= 2 * R; ++dx) {
+                            const T v = w[m + dx];
 #pragma unroll
-                        for (int q = 0; q < NQ; ++q) acc[q][i][m] = add_rn(acc[q][i][m], v);
-                    }
-            }
-        }
-        T* sp = reinterpret_cast<T*>(stage + (size_t)(pe & 1) * C::STAGE_BYTES) + s_off;
-#pragma unroll
-        for (int i = 0; i < PY; ++i) {
-            T o[PXV];
-#pragma unroll
-            for (int m = 0; m < PXV; ++m) {
-                o[m] = mul_rn(acc[0][i][m], avg);
-#pragma unroll
-                for (int q = 0; q + 1 < NQ; ++q) acc[q][i][m] = acc[q + 1][i][m];
-                acc[NQ - 1][i][m] = T(0);
-            }
-            if (storing && (s_rows & (1u << i))) {
-                VecN<T, PXV>::st(sp + i * C::VX, o);
-                if (x_tail && gy + i < g.n[1]) {  // the ragged end of the rows (tma3d.cuh)
-                    T* gp = out + g.idx(gx, gy + i, z_first + pe);
-#pragma unroll
-                    for (int k = 0; k < PXV; ++k)
-                        if (x_tail & (1u << k)) gp[k] = o[k];
+                            for (int q = 0; q < NQ; ++q) acc[q][i][m] = add_rn(acc[q][i][m], v);
+                        }
                 }
             }
-        }
+            T* sp = reinterpret_cast<T*>(stage + (size_t)(pe & 1) * C::STAGE_BYTES) + s_off;
+#pragma unroll
+            for (int i = 0; i < PY; ++i) {
+                T o[PXV];
+#pragma unroll
+                for (int m = 0; m < PXV; ++m) {
+                    o[m] = mul_rn(acc[0][i][m], avg);
+#pragma unroll
+                    for (int q = 0; q + 1 < NQ; ++q) acc[q][i][m] = acc[q + 1][i][m];
+                    acc[NQ - 1][i][m] = T(0);
+                }
+                if (storing && (s_rows & (1u << i))) {
+                    VecN<T, PXV>::st(sp + i * C::VX, o);
+                    if (x_tail && gy + i < g.n[1]) {  // the ragged end of the rows (tma3d.cuh)
+                        T* gp = out + g.idx(gx, gy + i, z_first + pe);
+#pragma unroll
+                        for (int k = 0; k < PXV; ++k)
+                            if (x_tail & (1u << k)) gp[k] = o[k];
+                    }
+                }
+            }
         }  // warp_on
         if (storing) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         if (tid == 0) tma_store_wait_read();
