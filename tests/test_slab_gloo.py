@@ -122,14 +122,14 @@ class OracleEngine:
         return _NullCtx()
 
 
-def _worker(rank, world, port, n, shape, dtype, T, k, out, exchange="nccl"):
+def _worker(rank, world, port, n, shape, dtype, T, k, out, exchange="nccl", radius=1):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         ln = list(n)
         ln[-1] //= world
-        d = capi.make_desc(ln, 1, shape, dtype, T, time_block=k)
+        d = capi.make_desc(ln, radius, shape, dtype, T, time_block=k)
         sw = slab.SlabSweep(d, rank, world, engine_factory=OracleEngine, dist=dist, exchange=exchange)
         assert sw.exchange == exchange
         sw.fill(capi.INIT_RANDOM, seed=4)
@@ -170,6 +170,23 @@ def test_slab_linked_flow_matches_single_grid(tmp_path, world, n, T, k):
     got = np.load(out)
     want = oracle.run(n, 1, oracle.STAR, T, oracle.F64, oracle.INIT_RANDOM, 4)
     assert np.array_equal(got.view(np.uint8), want[1:-1].view(np.uint8))
+
+
+@pytest.mark.parametrize("world,n,r,shape,dtype,T", [
+    (2, (14, 12, 24), 2, capi.BOX, capi.F32, 4),      # 125-point box (tma3db): faces are r planes, one step per launch
+    (2, (16, 10, 20), 2, capi.STAR, capi.F64, 5),     # 13-point star (tma3dr)
+    (3, (20, 36), 3, capi.BOX, capi.F64, 3),          # 49-point box (warp2dr), three ranks
+])
+def test_slab_linked_flow_radius_kernels(tmp_path, world, n, r, shape, dtype, T):
+    """The linked flow at radius > 1 (ghost depth r * k, k = 1 for these families) against the
+    single-grid oracle."""
+    out = str(tmp_path / "res.npy")
+    port = 33500 + os.getpid() % 2000
+    mp.spawn(_worker, args=(world, port, n, shape, dtype, T, 1, out, "p2p", r), nprocs=world, join=True)
+    got = np.load(out)
+    code = oracle.F64 if dtype == capi.F64 else oracle.F32
+    want = oracle.run(n, r, oracle.STAR if shape == capi.STAR else oracle.BOX, T, code, oracle.INIT_RANDOM, 4)
+    assert np.array_equal(got.view(np.uint8), want[r:-r].view(np.uint8))
 
 
 def test_exchange_mode_selection():
