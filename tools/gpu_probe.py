@@ -59,6 +59,10 @@ if "c4" in which:
     for k in (1, 2, 4, 6):
         run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 48, capi.KERNEL_WARP2D, k)
     run("c4-9pt-f32", (16384, 16384), capi.BOX, capi.F32, 6, capi.KERNEL_GENERIC, 1)
+if "c1k" in which:  # config 1: every fused depth
+    for dt, nm in ((capi.F64, "f64"), (capi.F32, "f32")):
+        for k in (1, 2, 3, 4, 5, 6):
+            run(f"c1-{nm}", (4096, 4096), capi.STAR, dt, 120, capi.KERNEL_WARP2D, k)
 if "c1tile" in which:  # config 1 (and its fp32 twin): rows per warp (SB200_FLAG_BLOCK_TILE) against the planner's choice
     for dt, nm in ((capi.F64, "f64"), (capi.F32, "f32")):
         for k in (4, 6):
