@@ -782,7 +782,10 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     info->launches = (steps + c.k - 1) / c.k;
     const int k = steps && steps < (uint32_t)c.k ? (int)steps : c.k;
     if (c.kernel == SB200_KERNEL_WARP2D) {
-        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r, tile_pref(desc));
+        // the launcher's own number when a device is bound (it lengthens chunks to fit one round of
+        // resident warps); without one the report is the device-independent base geometry
+        const int resident = !g_group.empty() && g.r == 1 ? warp2d_resident_warps(es, t3_shape(desc), k) : 0;
+        const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r, tile_pref(desc), resident);
         info->tiles_x = (uint32_t)p.nstrips;
         info->tiles_y = 1;
         info->chunks = (uint32_t)p.nchunks;

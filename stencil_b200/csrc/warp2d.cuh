@@ -354,7 +354,12 @@ struct W2dPlan {
 // that way and a launch costs the latency of ONE warp walking its chunk row by row, so they
 // are cut into short chunks (>= 4 rows) until every SM sub-partition has a few warps.
 // R > 1: the radius-R kernel of warp2dr.cuh, whose halo is K*R per side.
-static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count, int R = 1, int prefer_rows = 0) {
+// resident_warps (0 = unknown): warps of this kernel one SM holds at once.  A grid that needs between
+// one and two rounds of them (config 1: 2240 items for 1776 places) runs a nearly empty second round;
+// its chunks are lengthened until the items fit ONE round (config 1 fp64: +10 % at k=4, +16 % at k=6,
+// profiles/r02t_c1_tile_probe.log).  Grids of many rounds keep their short chunks (config 4).
+static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count, int R = 1, int prefer_rows = 0,
+                               int resident_warps = 0) {
     W2dPlan p;
     const int V = (W2D_WIDTH - ((K * R + 3) & ~3) - K * R) & ~3;
     p.nstrips = (int)((nx + V - 1) / V);
@@ -378,6 +383,12 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
         chunk_rows = (rows + nchunks - 1) / nchunks;
         if (chunk_rows < 4) chunk_rows = 4;
     }
+    if (resident_warps > 0 && !small) {
+        const long long places = (long long)sm_count * resident_warps;
+        const long long items = ((rows + chunk_rows - 1) / chunk_rows) * p.nstrips;
+        const long long fit = places / p.nstrips;  // chunks per strip that fill one round
+        if (items > places && items < 2 * places && fit >= 1) chunk_rows = (rows + fit - 1) / fit;
+    }
     if (prefer_rows > 0) chunk_rows = prefer_rows;  // the caller's tile preference wins
     if (chunk_rows > rows) chunk_rows = rows;
     if (chunk_rows < 1) chunk_rows = 1;
@@ -387,11 +398,26 @@ static inline W2dPlan w2d_plan(long long nx, long long rows, int K, int sm_count
     return p;
 }
 
+// Warps of sweep_warp2d_kernel<T, SHAPE, K> one SM holds (occupancy API; 0 without a device).
+template <class T, int SHAPE, int K>
+static int w2d_resident_warps() {
+    static const int resident = [] {
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, sweep_warp2d_kernel<T, SHAPE, K, false>, 32 * W2D_WARPS, 0) !=
+            cudaSuccess) {
+            (void)cudaGetLastError();
+            return 0;
+        }
+        return nb * W2D_WARPS;
+    }();
+    return resident;
+}
+
 template <class T, int SHAPE, int K>
 static cudaError_t launch_warp2d_k(const T* in, T* out, const Grid& g, Domain dom, long long ob,
                                    long long oe, const Tuning& tn, cudaStream_t st, const SlabLinkDev* link_in) {
     if (oe <= ob) return cudaSuccess;
-    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, 1, tn.prefer_chunk);
+    const W2dPlan p = w2d_plan(g.n[0], oe - ob, K, tn.sm_count, 1, tn.prefer_chunk, w2d_resident_warps<T, SHAPE, K>());
     const T avg = Avg<T>::value(SHAPE == BOXSEP ? (int)BOX : SHAPE, 2, 1);
     if (link_in && (link_in->link_lo || link_in->link_hi)) {
         SlabLinkDev link = *link_in;
