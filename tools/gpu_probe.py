@@ -63,6 +63,10 @@ if "c1k" in which:  # config 1: every fused depth
     for dt, nm in ((capi.F64, "f64"), (capi.F32, "f32")):
         for k in (1, 2, 3, 4, 5, 6):
             run(f"c1-{nm}", (4096, 4096), capi.STAR, dt, 120, capi.KERNEL_WARP2D, k)
+if "star64" in which:  # fp64 5-point star at other sizes: default depth 4 against 6
+    for n in ((2048, 2048), (8192, 8192), (16384, 8192), (3000, 5000)):
+        for k in (4, 6):
+            run("5pt-f64", n, capi.STAR, capi.F64, 120, capi.KERNEL_WARP2D, k)
 if "c1tile" in which:  # config 1 (and its fp32 twin): rows per warp (SB200_FLAG_BLOCK_TILE) against the planner's choice
     for dt, nm in ((capi.F64, "f64"), (capi.F32, "f32")):
         for k in (4, 6):
