@@ -784,7 +784,9 @@ int sb200_plan(const sb200_desc* desc, uint32_t steps, int sm_count, sb200_plan_
     if (c.kernel == SB200_KERNEL_WARP2D) {
         // the launcher's own number when a device is bound (it lengthens chunks to fit one round of
         // resident warps); without one the report is the device-independent base geometry
-        const int resident = !g_group.empty() && g.r == 1 ? warp2d_resident_warps(es, t3_shape(desc), k) : 0;
+        // (SB200_PLAN_RESIDENT_WARPS stands in for the device's answer when planning without one: CPU tests)
+        const char* rw = getenv("SB200_PLAN_RESIDENT_WARPS");
+        const int resident = g.r != 1 ? 0 : !g_group.empty() ? warp2d_resident_warps(es, t3_shape(desc), k) : rw ? atoi(rw) : 0;
         const W2dPlan p = w2d_plan(g.n[0], g.n[1], k, sm_count, g.r, tile_pref(desc), resident);
         info->tiles_x = (uint32_t)p.nstrips;
         info->tiles_y = 1;

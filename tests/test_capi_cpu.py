@@ -105,6 +105,20 @@ def test_plan_host_logic(monkeypatch):
     p = capi.plan(capi.make_desc((400, 400), 3, capi.BOX, capi.F32, 100), 100)
     assert (p.kernel, p.time_block, p.launches) == (capi.KERNEL_WARP2D, 1, 100)  # 49-point box: warp kernel, one level
     assert capi.plan(capi.make_desc((400, 400), 5, capi.BOX, capi.F32, 100), 100).kernel == capi.KERNEL_GENERIC
+    # config 1 in fp64 (k=4: 160 registers, 12 resident warps per SM): 64-row chunks would make 2240 warp items for
+    # 1776 places — a full round and a nearly empty one; the planner lengthens the chunks to fit one round.  With 16
+    # resident warps (2368 places) the items already fit, and config 4's many rounds keep their short chunks.
+    c1 = capi.make_desc((4096, 4096), 1, capi.STAR, capi.F64, 100)
+    base = capi.plan(c1, 100)
+    assert (base.tiles_x, base.chunk_extent, base.chunks) == (35, 64, 64)
+    monkeypatch.setenv("SB200_PLAN_RESIDENT_WARPS", "12")
+    fit = capi.plan(c1, 100)
+    assert (fit.tiles_x, fit.chunk_extent, fit.chunks) == (35, 82, 50) and fit.tiles_x * fit.chunks <= 148 * 12
+    c4 = capi.make_desc((16384, 16384), 1, capi.BOX, capi.F32, 100)
+    assert capi.plan(c4, 100).chunk_extent == 160
+    monkeypatch.setenv("SB200_PLAN_RESIDENT_WARPS", "16")
+    assert capi.plan(c1, 100).chunk_extent == 64 and capi.plan(c4, 100).chunk_extent == 160
+    monkeypatch.delenv("SB200_PLAN_RESIDENT_WARPS")
     # 125-point box (3-D radius 2): TMA kernel, one step per launch; fp64 tiles store 60 x 60, fp32 tiles
     # 120 x 60 or 56 x 124, whichever computes fewer columns for this row length
     p = capi.plan(capi.make_desc((512, 512, 512), 2, capi.BOX, capi.F64, 4), 4)
